@@ -1,0 +1,189 @@
+/* pupil_b200.h — C ABI of libpupil_b200.so, the B200-native wavefront path tracer that replaces
+ * the OptiX pipeline of vymv/PupilOptixLab's example/path_tracer.
+ *
+ * Every entry point cites the reference interface it stands in for (paths are into the reference
+ * tree).  Plain C: opaque context, POD structs, pointers + sizes, int status codes.  No torch, no
+ * C++ types.  Calls on one context must be serialised by the caller (the reference serialises
+ * Pass::OnRun and SetScene under m_render_system_mutex, framework/system/system.cpp:96-101,142).
+ *
+ * The same header is implemented twice:
+ *   - PB_API symbols  pb_*   : the product, CUDA sm_100a (pupiloptixlab_b200/csrc)
+ *   - oracle symbols  orc_*  : the CPU oracle (oracle/), generated from the same prototypes with
+ *                              the prefix swapped — test infrastructure only.
+ */
+#ifndef PUPIL_B200_H
+#define PUPIL_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef PB_API
+#define PB_API __attribute__((visibility("default")))
+#endif
+
+/* ---- status codes ---------------------------------------------------------------------------- */
+enum {
+    PB_OK = 0,
+    PB_ERR_INVALID = 1,   /* bad argument / call order                         */
+    PB_ERR_CUDA = 2,      /* a CUDA runtime call failed (see pb_last_error)    */
+    PB_ERR_NO_DEVICE = 3, /* no CUDA device: there is NO CPU fallback          */
+    PB_ERR_LIMIT = 4,     /* a structural limit was exceeded (BVH depth, ...)  */
+    PB_ERR_NOT_COMMITTED = 5
+};
+
+/* ---- textures: mirror of Pupil::util::Texture / cuda::Texture -------------------------------
+ * framework/util/texture.h:22-26 (ETextureType), framework/cuda/texture.h:9-57.                 */
+enum { PB_TEX_RGB = 0, PB_TEX_BITMAP = 1, PB_TEX_CHECKERBOARD = 2 };
+
+typedef struct pb_texture {
+    uint32_t type;       /* PB_TEX_*                                                           */
+    float a[3];          /* rgb  | checkerboard patch1                                          */
+    float b[3];          /* ---  | checkerboard patch2                                          */
+    float uv_r0[4];      /* rows r0, r1 of the 4x4 uv transform (cuda/texture.h:34-36)          */
+    float uv_r1[4];
+    /* bitmap (row-major RGBA float, host pointer, copied at pb_add_material / pb_add_* time)   */
+    const float* bitmap;
+    uint32_t bitmap_w, bitmap_h;
+    uint32_t address_mode; /* 0 wrap, 1 clamp, 2 mirror, 3 border (util/texture.h)              */
+    uint32_t filter_mode;  /* 0 point, 1 linear                                                 */
+} pb_texture;
+
+/* ---- materials: mirror of Pupil::resource::Material (framework/resource/material.h:20-84) ----
+ * type values follow EMatType (framework/render/material/predefine.h:15-22 with
+ * framework/decl/material_decl.inl:4-11).                                                       */
+enum {
+    PB_MAT_DIFFUSE = 1,
+    PB_MAT_DIELECTRIC = 2,
+    PB_MAT_ROUGH_DIELECTRIC = 3,
+    PB_MAT_CONDUCTOR = 4,
+    PB_MAT_ROUGH_CONDUCTOR = 5,
+    PB_MAT_PLASTIC = 6,
+    PB_MAT_ROUGH_PLASTIC = 7
+};
+
+typedef struct pb_material {
+    uint32_t type;     /* PB_MAT_*                                                              */
+    uint32_t twosided; /* resource::Material::twosided                                          */
+    float int_ior, ext_ior;
+    uint32_t nonlinear;
+    uint32_t _pad;
+    pb_texture reflectance;            /* diffuse.reflectance | plastic.diffuse_reflectance      */
+    pb_texture specular_reflectance;
+    pb_texture specular_transmittance;
+    pb_texture alpha;
+    pb_texture eta;                    /* conductors                                             */
+    pb_texture k;
+} pb_material;
+
+/* ---- shape flags (resource::ShapeInstance, framework/resource/shape.h:60-72) ----------------- */
+enum { PB_SHAPE_FLIP_NORMALS = 1u, PB_SHAPE_FLIP_TEX_COORDS = 2u };
+
+/* ---- environment emitter (framework/resource/emitter.h, framework/world/emitter.cpp:280-313) - */
+enum { PB_ENV_NONE = 0, PB_ENV_CONSTANT = 1, PB_ENV_MAP = 2 };
+typedef struct pb_env {
+    uint32_t type;
+    float radiance[3];    /* constant                                                            */
+    float scale;          /* envmap                                                              */
+    float to_world[12];   /* envmap, rows of the 3x4                                             */
+    pb_texture map;       /* envmap bitmap                                                       */
+} pb_env;
+
+/* ---- rays / hits for the ray-cast entry points ------------------------------------------------ */
+typedef struct pb_ray { float ox, oy, oz, tmin, dx, dy, dz, tmax; } pb_ray;   /* 32 B */
+/* prim = global primitive id (insertion order: triangles of each mesh in index order, one per
+ * sphere); 0xFFFFFFFF = miss.  u,v = barycentric weights of vertices 1 and 2 (the layout of
+ * optixGetTriangleBarycentrics, framework/render/geometry.h:52), 0 for spheres.                  */
+typedef struct pb_hit { float t, u, v; uint32_t prim; } pb_hit;               /* 16 B */
+#define PB_MISS 0xFFFFFFFFu
+
+/* ---- render parameters: Pupil::pt::OptixLaunchParams::config + seeds (path_tracer/type.h:9-33) */
+typedef struct pb_render_params {
+    uint32_t width, height;
+    uint32_t max_depth;     /* config.max_depth                                                  */
+    uint32_t first_sample;  /* random_seed of the first frame rendered by this call              */
+    uint32_t sample_count;  /* number of frames (1 frame = 1 spp, pt_pass.cpp:51-56)             */
+    uint32_t sample_stride; /* frame index step (multi-GPU sample interleave); 0 means 1         */
+    uint32_t flags;         /* PB_RENDER_*                                                       */
+    uint32_t _pad;
+} pb_render_params;
+enum {
+    PB_RENDER_HOST_BUFFERS = 1u, /* output pointers are host memory (copy included in the call)  */
+    PB_RENDER_CLEAR = 2u         /* zero the sum buffer first (sample_cnt = 0, pt_pass.cpp:43)   */
+};
+
+typedef struct pb_stats {
+    uint64_t rays_closest, rays_any;        /* rays issued by the last render / trace call       */
+    uint64_t samples;                       /* pixel-samples finished                            */
+    uint64_t node_visits, prim_tests_tri, prim_tests_sphere; /* only from *_counted calls        */
+    uint64_t n_prims, n_nodes, n_emitters;
+    uint32_t bvh_depth, n_objects;
+    float    build_ms, last_render_ms, last_trace_ms;
+    uint32_t kernel_launches;               /* product kernels launched by the last call         */
+} pb_stats;
+
+typedef struct pb_ctx pb_ctx;
+
+/* ---- lifetime.  Replaces cuda::Context::Init + optix::Context::Init + PTPass ctor
+ * (framework/cuda/context.cpp:9-49, framework/optix/context.cpp:38-50, path_tracer/pt_pass.cpp:29) */
+PB_API int pb_create(pb_ctx** out, int device);
+PB_API void pb_destroy(pb_ctx* ctx);
+PB_API const char* pb_last_error(const pb_ctx* ctx);
+PB_API const char* pb_version(void);
+
+/* ---- scene ingestion: host pointers, copied during the call.  Replaces World::LoadScene →
+ * RenderObject ctor + Material::LoadMaterial + EmitterHelper::AddAreaEmitter + GAS::Create
+ * (framework/world/world.cpp:101-139, world/render_object.cpp:10-39,
+ *  render/material/optix_material.cpp:121-132, world/emitter.cpp:245-278, world/gas_manager.cpp:61). */
+PB_API int pb_scene_begin(pb_ctx* ctx);
+PB_API int pb_add_material(pb_ctx* ctx, const pb_material* m, uint32_t* out_id);
+/* pos: 3*n_vert, nrm: 3*n_vert or NULL, uv: 2*n_vert or NULL, idx: 3*n_tri; to_world = rows 0..2
+ * of the row-major Mat4 (framework/util/type.h:73).  area_radiance != NULL makes it an emitter.  */
+PB_API int pb_add_trimesh(pb_ctx* ctx, const float* pos, const float* nrm, const float* uv,
+                          uint32_t n_vert, const uint32_t* idx, uint32_t n_tri,
+                          const float to_world[12], uint32_t flags, uint32_t material,
+                          const pb_texture* area_radiance, uint32_t* out_object);
+/* unit sphere at the origin under to_world (shape.cpp:106-125 folds radius/center into it)       */
+PB_API int pb_add_sphere(pb_ctx* ctx, const float to_world[12], uint32_t flags, uint32_t material,
+                         const pb_texture* area_radiance, uint32_t* out_object);
+PB_API int pb_set_env(pb_ctx* ctx, const pb_env* env);
+/* optix::Camera (framework/render/camera.h:7-10): two row-major 4x4                              */
+PB_API int pb_set_camera(pb_ctx* ctx, const float sample_to_camera[16], const float camera_to_world[16]);
+/* emitter tables (EmitterHelper::ComputeProbability, world/emitter.cpp:321-337) + device BVH
+ * build (replaces optixAccelBuild, world/gas_manager.cpp:151, world/ias_manager.cpp:84)          */
+PB_API int pb_scene_commit(pb_ctx* ctx);
+/* IAS::Update analogue (world/ias_manager.cpp:116-151): new transform, then rebuild on device    */
+PB_API int pb_update_instance(pb_ctx* ctx, uint32_t object, const float to_world[12]);
+
+/* ---- ray casting.  Replaces optixTrace ray type 0 (path_tracer/main.cu:77,158) and ray type 1
+ * with TERMINATE_ON_FIRST_HIT (framework/render/emitter.h:91-100).  rays/hits are DEVICE pointers
+ * unless host != 0 (then the call stages them through the device, copies included).              */
+PB_API int pb_trace_closest(pb_ctx* ctx, const pb_ray* rays, uint64_t n, pb_hit* hits, int host, void* cuda_stream);
+PB_API int pb_trace_any(pb_ctx* ctx, const pb_ray* rays, uint64_t n, uint8_t* occluded, int host, void* cuda_stream);
+/* same result, instrumented build: fills node/prim visit counters in pb_stats (never timed)      */
+PB_API int pb_trace_closest_counted(pb_ctx* ctx, const pb_ray* rays, uint64_t n, pb_hit* hits, int host, void* cuda_stream);
+PB_API int pb_trace_any_counted(pb_ctx* ctx, const pb_ray* rays, uint64_t n, uint8_t* occluded, int host, void* cuda_stream);
+
+/* ---- render.  Replaces PTPass::OnRun → optix::Pass::Run → optixLaunch(w,h,1) repeated
+ * sample_count times (path_tracer/pt_pass.cpp:39-57, framework/optix/pass.h:69-87).
+ * accum_sum_rgba: w*h float4, receives SUMS of per-frame radiance in .xyz and the number of frames
+ * added in .w (the reference's running mean main.cu:187-193 is sum/count); albedo/normal: w*h*3
+ * floats of the last frame (main.cu:94-99) or NULL.                                              */
+PB_API int pb_render(pb_ctx* ctx, const pb_render_params* p, float* accum_sum_rgba, float* albedo_rgb,
+                     float* normal_rgb, void* cuda_stream);
+/* "frame buffer" of the reference: mean = sum.xyz / sum.w, alpha 1 (main.cu:192-193)             */
+PB_API int pb_resolve(pb_ctx* ctx, const float* accum_sum_rgba, float* frame_rgba, uint32_t n_pixels,
+                      int host, void* cuda_stream);
+
+PB_API int pb_get_stats(pb_ctx* ctx, pb_stats* out);
+
+/* ---- BVH export (test / roofline accounting only): the committed 8-wide BVH and its primitive
+ * records, host buffers.  Query sizes by passing NULL pointers.                                  */
+PB_API int pb_export_bvh(pb_ctx* ctx, void* nodes80, uint64_t* n_nodes, void* prims48, uint64_t* n_prims);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PUPIL_B200_H */

@@ -1,0 +1,201 @@
+"""Procedural inputs for tests and benchmarks: camera matrices, the reference's built-in meshes,
+the Cornell-box configs (C1/C2), the displaced-mesh + spheres scene (C3/C4/C5) and ray sets.
+
+Everything here only *describes* a scene through the C ABI (`capi.Context`); it works unchanged on
+the CUDA product and on the test oracle because both export the same entry points.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import capi
+
+# ------------------------------------------------------------------------------------------------
+# camera / transform math (restated from the public DirectXMath definitions)
+
+
+def perspective_sample_to_camera(fov_y_deg: float, aspect: float, near: float = 0.01, far: float = 10000.0) -> np.ndarray:
+    """util::Camera::GetSampleToCameraMatrix (framework/util/camera.cpp:7-20):
+    transpose(inverse(PerspectiveFovRH * Translation(1,1,0) * Scaling(.5,.5,1))), row-vector maths."""
+    fov = np.float32(fov_y_deg) / np.float32(180.0) * np.float32(3.14159265358979323846)
+    h = 1.0 / np.tan(np.float64(fov) * 0.5)
+    w = h / np.float64(aspect)
+    r = far / (near - far)
+    proj = np.array([[w, 0, 0, 0], [0, h, 0, 0], [0, 0, r, -1], [0, 0, r * near, 0]], np.float64)
+    T = np.eye(4)
+    T[3, :3] = (1, 1, 0)
+    S = np.diag([0.5, 0.5, 1.0, 1.0])
+    M = proj @ T @ S
+    return np.linalg.inv(M).T.astype(np.float32)
+
+
+def fov_x_to_y(fov_deg: float, width: int, height: int) -> float:
+    """framework/resource/scene.cpp:122-127 (fov_axis = x)."""
+    aspect = np.float32(height) / np.float32(width)
+    radian = np.float32(fov_deg) * np.float32(3.14159265358979323846) / np.float32(180.0) * np.float32(0.5)
+    t = np.float32(np.tan(radian)) * aspect
+    return float(np.float32(2.0) * np.float32(np.arctan(t)) * np.float32(180.0) / np.float32(3.14159265358979323846))
+
+
+def _flip_xz(m: np.ndarray) -> np.ndarray:
+    m = m.copy()
+    m[:3, 0] *= -1
+    m[:3, 2] *= -1
+    return m
+
+
+def lookat_to_world(origin, target, up) -> np.ndarray:
+    """Transform::LookAt (framework/util/transform.cpp:86-98) followed by the column flip of
+    LoadTransform3D (framework/resource/xml/util_loader.cpp:161-166)."""
+    e, f, u = (np.asarray(v, np.float64) for v in (origin, target, up))
+    z = e - f
+    z /= np.linalg.norm(z)
+    x = np.cross(u, z)
+    x /= np.linalg.norm(x)
+    y = np.cross(z, x)
+    m = np.eye(4)
+    m[:3, 0], m[:3, 1], m[:3, 2], m[:3, 3] = x, y, z, e
+    return _flip_xz(m).astype(np.float32)
+
+
+def sensor_to_world(to_world: np.ndarray) -> np.ndarray:
+    """The sensor case flips columns 0 and 2 (again) — framework/resource/scene.cpp:134-139."""
+    return _flip_xz(np.asarray(to_world, np.float32).reshape(4, 4))
+
+
+def set_perspective_camera(ctx: capi.Context, fov_deg, width, height, to_world_xml, fov_axis="x"):
+    fov_y = fov_x_to_y(fov_deg, width, height) if fov_axis == "x" else fov_deg
+    s2c = perspective_sample_to_camera(fov_y, np.float32(width) / np.float32(height))
+    c2w = sensor_to_world(to_world_xml)
+    ctx.set_camera(s2c, c2w)
+    return s2c, c2w
+
+
+def scale(sx, sy, sz):
+    return np.diag([sx, sy, sz, 1.0]).astype(np.float32)
+
+
+def translate(x, y, z):
+    m = np.eye(4, dtype=np.float32)
+    m[:3, 3] = (x, y, z)
+    return m
+
+
+def rotate(ux, uy, uz, angle_deg):
+    """Transform::Rotate quaternion form (framework/util/transform.cpp:7-47)."""
+    n = np.sqrt(ux * ux + uy * uy + uz * uz)
+    ux, uy, uz = ux / n, uy / n, uz / n
+    th = angle_deg / 180.0 * np.pi
+    a, s = np.cos(0.5 * th), np.sin(0.5 * th)
+    b, c, d = s * ux, s * uy, s * uz
+    m = np.eye(4)
+    m[:3, :3] = [[1 - 2 * c * c - 2 * d * d, 2 * b * c - 2 * a * d, 2 * a * c + 2 * b * d],
+                 [2 * b * c + 2 * a * d, 1 - 2 * b * b - 2 * d * d, 2 * c * d - 2 * a * b],
+                 [2 * b * d - 2 * a * c, 2 * a * b + 2 * c * d, 1 - 2 * b * b - 2 * c * c]]
+    return m.astype(np.float32)
+
+
+# ------------------------------------------------------------------------------------------------
+# built-in meshes (framework/resource/shape.cpp:20-66)
+
+RECT_POS = np.array([[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0]], np.float32)
+RECT_NRM = np.tile(np.array([[0, 0, 1]], np.float32), (4, 1))
+RECT_UV = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32)
+RECT_IDX = np.array([[0, 1, 2], [0, 2, 3]], np.uint32)
+
+
+def _cube():
+    faces = [  # (normal, 4 corners) in the reference's vertex order
+        ((-1, 0, 0), [(-1, -1, -1), (-1, -1, 1), (-1, 1, 1), (-1, 1, -1)]),
+        ((0, 0, -1), [(1, -1, -1), (-1, -1, -1), (-1, 1, -1), (1, 1, -1)]),
+        ((1, 0, 0), [(1, -1, 1), (1, -1, -1), (1, 1, -1), (1, 1, 1)]),
+        ((0, 0, 1), [(-1, -1, 1), (1, -1, 1), (1, 1, 1), (-1, 1, 1)]),
+        ((0, 1, 0), [(-1, 1, 1), (1, 1, 1), (1, 1, -1), (-1, 1, -1)]),
+        ((0, -1, 0), [(-1, -1, -1), (1, -1, -1), (1, -1, 1), (-1, -1, 1)]),
+    ]
+    pos = np.array([c for _, cs in faces for c in cs], np.float32)
+    nrm = np.array([n for n, cs in faces for _ in cs], np.float32)
+    uv = np.tile(RECT_UV, (6, 1))
+    idx = np.array([[4 * f + a, 4 * f + b, 4 * f + c] for f in range(6) for a, b, c in ((0, 1, 2), (0, 2, 3))], np.uint32)
+    return pos, nrm, uv, idx
+
+
+CUBE_POS, CUBE_NRM, CUBE_UV, CUBE_IDX = _cube()
+
+
+def add_rectangle(ctx, to_world, material, flags=0, area_radiance=None):
+    return ctx.add_trimesh(RECT_POS, RECT_NRM, RECT_UV, RECT_IDX, to_world, flags, material, area_radiance)
+
+
+def add_cube(ctx, to_world, material, flags=0, area_radiance=None):
+    return ctx.add_trimesh(CUBE_POS, CUBE_NRM, CUBE_UV, CUBE_IDX, to_world, flags, material, area_radiance)
+
+
+def add_sphere(ctx, center, radius, material, to_world=None, flags=0, area_radiance=None):
+    """ShapeLoader<_sphere> (shape.cpp:106-125,196-197): to_world * Translate(center) * Scale(radius)."""
+    m = translate(*center) @ scale(radius, radius, radius)
+    if to_world is not None:
+        m = np.asarray(to_world, np.float32).reshape(4, 4) @ m
+    return ctx.add_sphere(m.astype(np.float32), flags, material, area_radiance)
+
+
+# ------------------------------------------------------------------------------------------------
+# Cornell box: geometry of data/static/cornellbox.xml (the matrices are the XML's own values)
+
+def _m(s):
+    return np.array([float(x) for x in s.split()], np.float32).reshape(4, 4)
+
+
+CORNELL_SENSOR = _m("-1 0 0 0 0 1 0 1 0 0 -1 6.8 0 0 0 1")
+CORNELL = {
+    "Floor": ("rectangle", _m("-4.37114e-008 1 4.37114e-008 0 0 -8.74228e-008 2 0 1 4.37114e-008 1.91069e-015 0 0 0 0 1")),
+    "Ceiling": ("rectangle", _m("-1 7.64274e-015 -1.74846e-007 0 8.74228e-008 8.74228e-008 -2 2 0 -1 -4.37114e-008 0 0 0 0 1")),
+    "BackWall": ("rectangle", _m("1.91069e-015 1 1.31134e-007 0 1 3.82137e-015 -8.74228e-008 1 -4.37114e-008 1.31134e-007 -2 -1 0 0 0 1")),
+    "RightWall": ("rectangle", _m("4.37114e-008 -1.74846e-007 2 1 1 3.82137e-015 -8.74228e-008 1 3.82137e-015 1 2.18557e-007 0 0 0 0 1")),
+    "LeftWall": ("rectangle", _m("-4.37114e-008 8.74228e-008 -2 -1 1 3.82137e-015 -8.74228e-008 1 0 -1 -4.37114e-008 0 0 0 0 1")),
+    "ShortBox": ("cube", _m("0.0851643 0.289542 1.31134e-008 0.328631 3.72265e-009 1.26563e-008 -0.3 0.3 -0.284951 0.0865363 5.73206e-016 0.374592 0 0 0 1")),
+    "TallBox": ("cube", _m("0.286776 0.098229 -2.29282e-015 -0.335439 -4.36233e-009 1.23382e-008 -0.6 0.6 -0.0997984 0.282266 2.62268e-008 -0.291415 0 0 0 1")),
+    "Light": ("rectangle", _m("0.235 -1.66103e-008 -7.80685e-009 -0.005 -2.05444e-008 3.90343e-009 -0.0893 1.98 2.05444e-008 0.19 8.30516e-009 -0.03 0 0 0 1")),
+}
+WHITE = (0.725, 0.71, 0.68)
+
+
+def cornell_box(ctx: capi.Context, width=256, height=256, variant="diffuse") -> dict:
+    """C1 (variant='diffuse'): cornellbox.xml as shipped.  C2 (variant='materials'): walls keep their
+    diffuse BSDFs, the boxes and five added spheres carry the other six materials with the
+    parameters of data/static/material_test.xml:30-114."""
+    ctx.scene_begin()
+    M = capi.make_material
+    diff = lambda rgb: ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True, reflectance=rgb))
+    mats = {"Floor": diff(WHITE), "Ceiling": diff(WHITE), "BackWall": diff(WHITE),
+            "RightWall": diff((0.14, 0.45, 0.091)), "LeftWall": diff((0.63, 0.065, 0.05)),
+            "ShortBox": diff(WHITE), "TallBox": diff(WHITE), "Light": diff((0, 0, 0))}
+    if variant == "materials":
+        mats["ShortBox"] = ctx.add_material(M(capi.MAT_ROUGH_PLASTIC, int_ior=1.5, ext_ior=1.0, alpha=0.35,
+                                              reflectance=(0.647814,) * 3))
+        mats["TallBox"] = ctx.add_material(M(capi.MAT_ROUGH_CONDUCTOR, alpha=0.35, specular_reflectance=0.3,
+                                             eta=(0.200438, 0.924033, 1.10221), k=(3.91295, 2.45285, 2.14219)))
+        mats["Floor"] = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True,
+                                           reflectance=capi.checker_texture((0.725, 0.71, 0.68), (0.3, 0.3, 0.32), 8, 8)))
+    objs = {}
+    for name, (kind, m) in CORNELL.items():
+        ar = capi.rgb_texture(17, 12, 4) if name == "Light" else None
+        add = add_rectangle if kind == "rectangle" else add_cube
+        objs[name] = add(ctx, m, mats[name], 0, ar)
+    if variant == "materials":
+        sph = [
+            ((-0.55, 0.25, 0.55), 0.25, M(capi.MAT_DIELECTRIC, int_ior=1.5, ext_ior=1.0)),
+            ((0.0, 0.2, 0.7), 0.2, M(capi.MAT_ROUGH_DIELECTRIC, int_ior=1.5, ext_ior=1.0, alpha=0.35)),
+            ((0.6, 0.2, 0.65), 0.2, M(capi.MAT_PLASTIC, int_ior=1.5, ext_ior=1.0, reflectance=(0.647814,) * 3)),
+            ((0.33, 0.78, 0.37), 0.18, M(capi.MAT_CONDUCTOR, specular_reflectance=0.3,
+                                         eta=(0.200438, 0.924033, 1.10221), k=(3.91295, 2.45285, 2.14219))),
+            ((-0.34, 1.38, -0.29), 0.18, M(capi.MAT_ROUGH_CONDUCTOR, alpha=0.95, specular_reflectance=0.8,
+                                           eta=(0.15494, 0.11648, 0.13809), k=(4.81810, 3.11562, 2.14240))),
+        ]
+        for i, (c, r, mat) in enumerate(sph):
+            objs[f"sphere{i}"] = add_sphere(ctx, c, r, ctx.add_material(mat))
+        # a small emissive sphere exercises SphereEmitter (emitter/sphere.h)
+        objs["bulb"] = add_sphere(ctx, (0.7, 1.6, 0.4), 0.06, mats["Light"], area_radiance=capi.rgb_texture(30, 30, 30))
+    set_perspective_camera(ctx, 19.5, width, height, CORNELL_SENSOR)
+    ctx.commit()
+    return {"width": width, "height": height, "objects": objs, "materials": mats}
