@@ -1,0 +1,58 @@
+// pb_scene.cuh — scene geometry in HBM and the object-space -> world-space primitive kernel body.
+//
+// All meshes share four arrays (positions, normals, uvs as packed floats; indices as packed
+// uint32 triples); ObjRec holds the offsets.  This is the data World::LoadScene/RenderObject hand to
+// OptiX as per-shape GAS inputs + per-instance transforms (framework/world/render_object.cpp:10-39,
+// framework/world/gas_manager.cpp:79-131, framework/world/ias_manager.cpp:165-185); here instances
+// are flattened: one world-space PrimRec per triangle / sphere, global id = insertion order.
+#pragma once
+#include "pb_intersect.cuh"
+
+namespace pb {
+
+struct SceneGeom {
+    const float* pos;        // 3 floats per vertex
+    const float* nrm;        // 3 floats per vertex (garbage where the object has no normals)
+    const float* uv;         // 2 floats per vertex
+    const uint32_t* idx;     // 3 per triangle, object-local vertex numbers
+    const ObjRec* objs;
+    uint32_t n_objs;
+    uint32_t n_prims;
+};
+
+PB_HD uint32_t object_of_prim(const SceneGeom& g, uint32_t prim) {  // last object with prim_offset <= prim
+    uint32_t lo = 0, hi = g.n_objs;
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (g.objs[mid].prim_offset <= prim) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+PB_HD PrimRec make_prim(const SceneGeom& g, uint32_t prim) {
+    const uint32_t oi = object_of_prim(g, prim);
+    const ObjRec& o = g.objs[oi];
+    PrimRec r;
+    if (o.flags & OBJ_SPHERE) {
+        V3 r0 = {o.M[0], o.M[1], o.M[2]}, r1 = {o.M[4], o.M[5], o.M[6]}, r2 = {o.M[8], o.M[9], o.M[10]};
+        r.a = {o.M[3], o.M[7], o.M[11], u2f(prim)};
+        r.b = {f_sqrt(dot_fma(r0, r0)), f_sqrt(dot_fma(r1, r1)), f_sqrt(dot_fma(r2, r2)), u2f(oi)};
+        r.c = {0.f, 0.f, 0.f, u2f(PRIM_SPHERE)};
+    } else {
+        const uint32_t* t = g.idx + 3ull * (o.index_offset + (prim - o.prim_offset));
+        const float* p = g.pos + 3ull * o.vert_offset;
+        V3 v0 = xform_point_fma(o.M, {p[3 * t[0]], p[3 * t[0] + 1], p[3 * t[0] + 2]});
+        V3 v1 = xform_point_fma(o.M, {p[3 * t[1]], p[3 * t[1] + 1], p[3 * t[1] + 2]});
+        V3 v2 = xform_point_fma(o.M, {p[3 * t[2]], p[3 * t[2] + 1], p[3 * t[2] + 2]});
+        r.a = {v0.x, v0.y, v0.z, u2f(prim)};
+        r.b = {v1.x, v1.y, v1.z, u2f(oi)};
+        r.c = {v2.x, v2.y, v2.z, u2f(PRIM_TRI)};
+    }
+    return r;
+}
+
+// monotone float <-> uint mapping for atomicMin/atomicMax reductions of the scene box
+PB_HD uint32_t float_to_ordered(float f) { uint32_t u = f2u(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+PB_HD float ordered_to_float(uint32_t u) { return u2f((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
+
+}  // namespace pb

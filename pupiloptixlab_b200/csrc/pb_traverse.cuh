@@ -1,0 +1,163 @@
+// pb_traverse.cuh — closest-hit / any-hit traversal of the compressed 8-wide BVH.
+//
+// Replaces optixTrace (example/path_tracer/main.cu:77-82,158-163: ray type 0, closest hit) and
+// Emitter::TraceShadowRay (framework/render/emitter.h:91-100: ray type 1, terminate on first hit).
+//
+// One ray per lane.  Node = 5 x 128-bit loads, primitive = 3 x 128-bit loads (read-only path).
+// Traversal state is two 64-bit "groups" (Ylitie et al. 2017): G = (child base, inner-hit bits |
+// imask), P = (prim base, prim-hit bits); deferred node groups go to a per-lane stack whose first
+// PB_SMEM_STACK entries live in shared memory ([entry][lane] layout, conflict free) and spill to
+// local memory beyond that.  Children are visited front to back through the octant trick: the
+// builder places children in octant-ordered slots and bit (24 + (slot ^ octinv)) of the hit mask
+// orders them for this ray.
+//
+// Result = lexicographic min of (t, prim id) over accepted hits (pb_intersect.cuh), which is
+// independent of tree shape and visiting order; the node test below may therefore use folded
+// arithmetic (one FMA per plane): its rounding error is covered by the delta gap between B_in and B_out.
+#pragma once
+#include "pb_intersect.cuh"
+
+namespace pb {
+
+struct alignas(16) U4 { uint32_t x, y, z, w; };
+
+struct TraceScene {
+    const U4* nodes;      // Node8 as 5 x U4
+    const V4* prims;      // PrimRec as 3 x V4
+    const ObjRec* objs;
+    float delta;
+    uint32_t n_nodes;
+};
+
+struct Hit { float t, u, v; uint32_t prim; };
+struct TraceCounters { unsigned long long nodes, tris, spheres; };
+
+#if defined(__CUDA_ARCH__)
+PB_D U4 ld_u4(const U4* p) { uint4 r = __ldg(reinterpret_cast<const uint4*>(p)); return {r.x, r.y, r.z, r.w}; }
+PB_D V4 ld_v4(const V4* p) { float4 r = __ldg(reinterpret_cast<const float4*>(p)); return {r.x, r.y, r.z, r.w}; }
+PB_D int hi_bit(uint32_t x) { return 31 - __clz(x); }
+PB_D int lo_bit(uint32_t x) { return __ffs(x) - 1; }
+PB_D int pop_cnt(uint32_t x) { return __popc(x); }
+#else
+inline U4 ld_u4(const U4* p) { return *p; }
+inline V4 ld_v4(const V4* p) { return *p; }
+inline int hi_bit(uint32_t x) { return 31 - __builtin_clz(x); }
+inline int lo_bit(uint32_t x) { return __builtin_ctz(x); }
+inline int pop_cnt(uint32_t x) { return __builtin_popcount(x); }
+#endif
+
+#ifndef PB_SMEM_STACK
+#define PB_SMEM_STACK 8
+#endif
+#define PB_LOCAL_STACK 56
+
+struct U2 { uint32_t x, y; };
+
+// Per-lane traversal stack: shared-memory head + local-memory tail.
+struct LaneStack {
+    U2* smem;          // this lane's first entry; entries are `stride` apart
+    uint32_t stride;
+    U2 local[PB_LOCAL_STACK];
+    int sp;
+    PB_HD void init(U2* s, uint32_t st) { smem = s; stride = st; sp = 0; }
+    PB_HD void push(U2 v) {
+        if (sp < PB_SMEM_STACK) smem[sp * stride] = v;
+        else local[sp - PB_SMEM_STACK] = v;
+        ++sp;
+    }
+    PB_HD U2 pop() {
+        --sp;
+        return sp < PB_SMEM_STACK ? smem[sp * stride] : local[sp - PB_SMEM_STACK];
+    }
+};
+
+// hit mask of one node for this ray: bits 24..31 inner children (octant ordered), bits 0..23 prims
+PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3, const U4& n4, V3 o, const RayPre& pre,
+                         uint32_t octinv, float tmin, float tmax) {
+    // n0 = px py pz [ex ey ez imask]; n1 = child_base prim_base meta[0..3] meta[4..7]
+    // n2 = qlox[0..7] qloy[0..7]; n3 = qloz[0..7] qhix[0..7]; n4 = qhiy[0..7] qhiz[0..7]
+    const uint32_t e = n0.w;
+    const float sx = u2f((e & 0xffu) << 23), sy = u2f(((e >> 8) & 0xffu) << 23), sz = u2f(((e >> 16) & 0xffu) << 23);
+    const float ax = f_mul(sx, pre.id.x), ay = f_mul(sy, pre.id.y), az = f_mul(sz, pre.id.z);
+    const float bx = f_mul(f_sub(u2f(n0.x), o.x), pre.id.x);
+    const float by = f_mul(f_sub(u2f(n0.y), o.y), pre.id.y);
+    const float bz = f_mul(f_sub(u2f(n0.z), o.z), pre.id.z);
+    const bool nx = pre.id.x < 0.f, ny = pre.id.y < 0.f, nz = pre.id.z < 0.f;
+    uint32_t mask = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        const uint32_t meta4 = half ? n1.w : n1.z;
+        const uint32_t lx = half ? n2.y : n2.x, ly = half ? n2.w : n2.z, lz = half ? n3.y : n3.x;
+        const uint32_t hx = half ? n3.w : n3.z, hy = half ? n4.y : n4.x, hz = half ? n4.w : n4.z;
+        const uint32_t qnx = nx ? hx : lx, qfx = nx ? lx : hx;
+        const uint32_t qny = ny ? hy : ly, qfy = ny ? ly : hy;
+        const uint32_t qnz = nz ? hz : lz, qfz = nz ? lz : hz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t meta = (meta4 >> (8 * j)) & 0xffu;
+            if (meta == 0u) continue;
+            const int sh = 8 * j;
+            float tnx = f_fma((float)((qnx >> sh) & 0xffu), ax, bx), tfx = f_fma((float)((qfx >> sh) & 0xffu), ax, bx);
+            float tny = f_fma((float)((qny >> sh) & 0xffu), ay, by), tfy = f_fma((float)((qfy >> sh) & 0xffu), ay, by);
+            float tnz = f_fma((float)((qnz >> sh) & 0xffu), az, bz), tfz = f_fma((float)((qfz >> sh) & 0xffu), az, bz);
+            float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+            float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
+            if (tn <= tf) {
+                const uint32_t low5 = meta & 31u;
+                if (low5 >= 24u) mask |= 1u << (24u + ((low5 - 24u) ^ octinv));   // inner child
+                else mask |= (meta >> 5) << low5;                                  // leaf: unary count bits
+            }
+        }
+    }
+    return mask;
+}
+
+template<bool ANY, bool COUNT>
+PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hit& best, LaneStack& st, TraceCounters* cnt) {
+    best.t = tmax; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu;
+    if (sc.n_nodes == 0) return;
+    const RayPre pre = ray_pre(o, d);
+    const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
+    const uint32_t octinv = 7u - oct;
+    U2 G = {0u, 0x80000000u};
+    st.sp = 0;
+    while (true) {
+        U2 P = {0u, 0u};
+        if (G.y & 0xff000000u) {
+            const int bit = hi_bit(G.y);
+            const uint32_t imask = G.y & 0xffu;
+            G.y &= ~(1u << bit);
+            if (G.y & 0xff000000u) st.push(G);
+            const uint32_t slot = ((uint32_t)bit - 24u) ^ octinv;
+            const uint32_t rel = (uint32_t)pop_cnt(imask & ((1u << slot) - 1u));
+            const U4* np = sc.nodes + 5ull * (G.x + rel);
+            const U4 n0 = ld_u4(np), n1 = ld_u4(np + 1), n2 = ld_u4(np + 2), n3 = ld_u4(np + 3), n4 = ld_u4(np + 4);
+            if (COUNT) cnt->nodes++;
+            const uint32_t hits = node_hits(n0, n1, n2, n3, n4, o, pre, octinv, tmin, best.t);
+            G.x = n1.x;
+            G.y = (hits & 0xff000000u) | (n0.w >> 24);
+            P.x = n1.y;
+            P.y = hits & 0x00ffffffu;
+        }
+        while (P.y) {
+            const int i = lo_bit(P.y);
+            P.y &= P.y - 1u;
+            const V4* pp = sc.prims + 3ull * (P.x + (uint32_t)i);
+            PrimRec r;
+            r.a = ld_v4(pp); r.b = ld_v4(pp + 1); r.c = ld_v4(pp + 2);
+            if (COUNT) { if (f2u(r.c.w) == PRIM_TRI) cnt->tris++; else cnt->spheres++; }
+            float t, u, v;
+            if (prim_accept(r, sc.objs, o, d, pre, tmin, tmax, sc.delta, t, u, v)) {
+                const uint32_t id = f2u(r.a.w);
+                if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; return; }
+                if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; }
+            }
+        }
+        if (!(G.y & 0xff000000u)) {
+            if (st.sp == 0) break;
+            G = st.pop();
+        }
+    }
+}
+
+}  // namespace pb
