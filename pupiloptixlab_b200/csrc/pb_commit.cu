@@ -1,0 +1,174 @@
+// pb_commit.cu — pb_scene_commit / pb_update_instance / ray-cast / render / stats entry points.
+#include <chrono>
+#include <cstring>
+
+#include "pb_host_prep.h"
+#include "pb_internal.h"
+
+using namespace pb;
+void pb_free_device_scene(pb_ctx* c);
+
+#define PB_REQUIRE(cond, msg)                       \
+    do {                                            \
+        if (!(cond)) { c->err = (msg); return PB_ERR_INVALID; } \
+    } while (0)
+
+template<class T>
+static int upload(pb_ctx* c, T** dst, const std::vector<T>& src) {
+    *dst = nullptr;
+    PB_CUDA_TRY(c, cudaMalloc(dst, (src.empty() ? 1 : src.size()) * sizeof(T)));
+    if (!src.empty()) PB_CUDA_TRY(c, cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return PB_OK;
+}
+
+static bool uses_bitmap(const pb_material& m) {
+    return m.reflectance.type == PB_TEX_BITMAP || m.specular_reflectance.type == PB_TEX_BITMAP ||
+           m.specular_transmittance.type == PB_TEX_BITMAP || m.alpha.type == PB_TEX_BITMAP ||
+           m.eta.type == PB_TEX_BITMAP || m.k.type == PB_TEX_BITMAP;
+}
+
+// World::LoadScene -> RenderObject / EmitterHelper / ComputeProbability, then the device BVH build
+static int commit(pb_ctx* c) {
+    cudaSetDevice(c->device);
+    pb_free_device_scene(c);
+    c->stats = pb_stats{};
+    auto t0 = std::chrono::steady_clock::now();
+
+    // ---- materials
+    std::vector<MatRec> mats;
+    for (auto& m : c->materials) {
+        PB_REQUIRE(!uses_bitmap(m), "bitmap textures are not supported by this build (SURVEY 8f rank 2)");
+        mats.push_back(prep::mat_rec(m));
+    }
+    // ---- objects + emitters (emitter_index_offset: example/path_tracer/pt_pass.cpp:159-170)
+    c->h_objs.clear();
+    std::vector<EmitRec> emit;
+    uint32_t prim = 0;
+    int emitter_offset = 0;
+    for (auto& o : c->objects) {
+        ObjRec r{};
+        memcpy(r.M, o.M, 48);
+        invert_affine(r.M, r.Minv);
+        r.flags = (o.sphere ? OBJ_SPHERE : 0u) | ((o.flags & PB_SHAPE_FLIP_NORMALS) ? OBJ_FLIP_NORMALS : 0u) |
+                  ((o.flags & PB_SHAPE_FLIP_TEX_COORDS) ? OBJ_FLIP_TEX : 0u) | (o.has_nrm ? OBJ_HAS_NORMALS : 0u) |
+                  (o.has_uv ? OBJ_HAS_UV : 0u);
+        r.material = o.material;
+        r.prim_offset = prim;
+        r.vert_offset = o.vert_offset; r.index_offset = o.index_offset;
+        r.n_prims = o.sphere ? 1u : o.n_tri;
+        r.emitter_offset = -1;
+        if (o.is_emitter) {
+            PB_REQUIRE(o.area_radiance.type != PB_TEX_BITMAP, "bitmap radiance textures are not supported by this build");
+            r.emitter_offset = emitter_offset;
+            const float select_weight = prep::emitter_weight(o.area_radiance);
+            if (o.sphere) {  // SetSphereAreaEmitter, world/emitter.cpp:224-243
+                EmitRec e{};
+                e.type = EM_SPHERE;
+                const float p0[3] = {0.f, 0.f, 0.f}, p1[3] = {0.f + 1.f, 0.f, 0.f};
+                float ctr[3], px[3];
+                prep::transform_point(r.M, p0, ctr);
+                prep::transform_point(r.M, p1, px);
+                for (int k = 0; k < 3; ++k) e.p0[k] = ctr[k];
+                const float dx = ctr[0] - px[0], dy = ctr[1] - px[1], dz = ctr[2] - px[2];
+                const float radius = sqrtf(dx * dx + dy * dy + dz * dz);
+                e.p1[0] = radius;
+                e.area = 4 * 3.14159265358979323846f * radius * radius;
+                e.radiance = prep::tex_rec(o.area_radiance);
+                e.weight = select_weight * e.area;
+                emit.push_back(e);
+                emitter_offset += 1;
+            } else {  // SetMeshAreaEmitter, world/emitter.cpp:169-222
+                const float* P = c->h_pos.data() + 3ull * o.vert_offset;
+                const float* N = c->h_nrm.data() + 3ull * o.vert_offset;
+                const float* T = c->h_uv.data() + 2ull * o.vert_offset;
+                const uint32_t* I = c->h_idx.data() + 3ull * o.index_offset;
+                for (uint32_t f = 0; f < o.n_tri; ++f) {
+                    EmitRec e{};
+                    e.type = EM_TRI;
+                    float* pp[3] = {e.p0, e.p1, e.p2};
+                    float* nn[3] = {e.n0, e.n1, e.n2};
+                    float* tt[3] = {e.t0, e.t1, e.t2};
+                    for (int k = 0; k < 3; ++k) {
+                        const uint32_t vi = I[3 * f + k];
+                        prep::transform_point(r.M, P + 3 * vi, pp[k]);
+                        prep::transform_normal(r.Minv, N + 3 * vi, nn[k]);
+                        tt[k][0] = T[2 * vi]; tt[k][1] = T[2 * vi + 1];
+                    }
+                    const float ax = e.p1[0] - e.p0[0], ay = e.p1[1] - e.p0[1], az = e.p1[2] - e.p0[2];
+                    const float bx = e.p2[0] - e.p0[0], by = e.p2[1] - e.p0[1], bz = e.p2[2] - e.p0[2];
+                    const float cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+                    e.area = sqrtf(cx * cx + cy * cy + cz * cz) * 0.5f;
+                    e.radiance = prep::tex_rec(o.area_radiance);
+                    e.weight = select_weight * e.area;
+                    emit.push_back(e);
+                }
+                emitter_offset += (int)o.n_tri;
+            }
+        }
+        prim += r.n_prims;
+        c->h_objs.push_back(r);
+    }
+    c->n_area_emitters = (uint32_t)emit.size();
+
+    // ---- geometry upload + world-space primitives (gives the scene box needed by the env emitter)
+    if (upload(c, &c->d_pos, c->h_pos) || upload(c, &c->d_nrm, c->h_nrm) || upload(c, &c->d_uv, c->h_uv) ||
+        upload(c, &c->d_idx, c->h_idx) || upload(c, &c->d_objs, c->h_objs) || upload(c, &c->d_mats, mats))
+        return PB_ERR_CUDA;
+    PrimRec* d_prims_in = nullptr;
+    PB_CUDA_TRY(c, cudaMalloc(&d_prims_in, (prim ? prim : 1) * sizeof(PrimRec)));
+    int rc = make_world_prims(c, d_prims_in, c->stream);
+    if (rc == PB_OK) rc = build_bvh(c, d_prims_in, prim, c->stream);
+    cudaFree(d_prims_in);
+    if (rc != PB_OK) return rc;
+
+    // ---- environment emitter (AddEmitter, world/emitter.cpp:280-313) and select probabilities
+    c->has_env = false;
+    EmitRec env{};
+    if (c->env.type == PB_ENV_CONSTANT) {
+        env.type = EM_CONST_ENV;
+        for (int k = 0; k < 3; ++k) env.p0[k] = c->env.radiance[k];
+        V3 ctr = (c->scene_hi + c->scene_lo) * 0.5f;
+        env.p1[0] = ctr.x; env.p1[1] = ctr.y; env.p1[2] = ctr.z;
+        env.weight = 1.f;
+        c->has_env = true;
+    } else if (c->env.type == PB_ENV_MAP) {
+        c->err = "envmap emitters are not supported by this build (SURVEY 8f rank 2)";
+        return PB_ERR_INVALID;
+    }
+    // ComputeProbability, world/emitter.cpp:321-337
+    float area_weight_sum = 0.f;
+    for (auto& e : emit) area_weight_sum += e.weight;
+    if (!emit.empty())
+        for (auto& e : emit) e.select_probability = e.weight / area_weight_sum * emit.size();
+    const size_t emitter_num = (c->has_env ? 1 : 0) + emit.size();
+    for (auto& e : emit) e.select_probability = e.select_probability / emitter_num;
+    env.select_probability = env.weight / emitter_num;
+    std::vector<float> prefix(emit.size());
+    float sum_p = 0.f;
+    for (size_t i = 0; i < emit.size(); ++i) { prefix[i] = sum_p + emit[i].select_probability; sum_p += emit[i].select_probability; }
+    emit.push_back(env);  // slot n_area_emitters holds the env emitter (type EM_NONE when absent)
+    if (upload(c, &c->d_emit, emit) || upload(c, &c->d_emit_prefix, prefix)) return PB_ERR_CUDA;
+
+    c->stats.n_prims = prim; c->stats.n_nodes = c->n_nodes; c->stats.n_emitters = emitter_num;
+    c->stats.n_objects = (uint32_t)c->h_objs.size(); c->stats.bvh_depth = c->bvh_levels;
+    c->stats.build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->committed = true;
+    return PB_OK;
+}
+
+extern "C" {
+
+PB_API int pb_scene_commit(pb_ctx* c) {
+    if (!c) return PB_ERR_INVALID;
+    PB_REQUIRE(c->in_scene, "pb_scene_commit without pb_scene_begin");
+    return commit(c);
+}
+
+PB_API int pb_update_instance(pb_ctx* c, uint32_t object, const float to_world[12]) {
+    if (!c) return PB_ERR_INVALID;
+    PB_REQUIRE(object < c->objects.size(), "object id out of range");
+    memcpy(c->objects[object].M, to_world, 48);
+    return commit(c);   // LBVH rebuild on device is this framework's IAS::Update
+}
+
+}  // extern "C"

@@ -1,0 +1,141 @@
+// pb_entry.cu — ray-cast, render, resolve, stats and BVH-export entry points of the C ABI.
+#include <cstring>
+
+#include "pb_internal.h"
+
+using namespace pb;
+
+#define PB_REQUIRE(cond, msg)                       \
+    do {                                            \
+        if (!(cond)) { c->err = (msg); return PB_ERR_INVALID; } \
+    } while (0)
+
+static int trace_entry(pb_ctx* c, const pb_ray* rays, uint64_t n, void* out, int host, void* stream, bool any, bool counted) {
+    if (!c) return PB_ERR_INVALID;
+    if (!c->committed) { c->err = "scene not committed"; return PB_ERR_NOT_COMMITTED; }
+    PB_REQUIRE((rays && out) || n == 0, "null ray / result pointer");
+    cudaSetDevice(c->device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    const size_t out_bytes = any ? n : n * sizeof(pb_hit);
+    cudaEvent_t e0, e1;
+    PB_CUDA_TRY(c, cudaEventCreate(&e0)); PB_CUDA_TRY(c, cudaEventCreate(&e1));
+    int rc = PB_OK;
+    if (host) {
+        pb_ray* d_rays = nullptr; void* d_out = nullptr;
+        PB_CUDA_TRY(c, cudaMalloc(&d_rays, (n ? n : 1) * sizeof(pb_ray)));
+        PB_CUDA_TRY(c, cudaMalloc(&d_out, out_bytes ? out_bytes : 1));
+        PB_CUDA_TRY(c, cudaMemcpyAsync(d_rays, rays, n * sizeof(pb_ray), cudaMemcpyHostToDevice, s));
+        cudaEventRecord(e0, s);
+        rc = trace_rays(c, d_rays, n, any ? nullptr : (pb_hit*)d_out, any ? (uint8_t*)d_out : nullptr, any, counted, s);
+        cudaEventRecord(e1, s);
+        if (rc == PB_OK) {
+            cudaError_t e = cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+            if (e != cudaSuccess) { c->err = std::string("trace (host buffers): ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
+        }
+        cudaFree(d_rays); cudaFree(d_out);
+    } else {
+        cudaEventRecord(e0, s);
+        rc = trace_rays(c, rays, n, any ? nullptr : (pb_hit*)out, any ? (uint8_t*)out : nullptr, any, counted, s);
+        cudaEventRecord(e1, s);
+        if (rc == PB_OK) {
+            cudaError_t e = cudaStreamSynchronize(s);
+            if (e != cudaSuccess) { c->err = std::string("trace: ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
+        }
+    }
+    if (rc == PB_OK) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        c->stats.last_trace_ms = ms;
+        if (any) c->stats.rays_any = n; else c->stats.rays_closest = n;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return rc;
+}
+
+extern "C" {
+
+PB_API int pb_trace_closest(pb_ctx* c, const pb_ray* rays, uint64_t n, pb_hit* hits, int host, void* stream) {
+    return trace_entry(c, rays, n, hits, host, stream, false, false);
+}
+PB_API int pb_trace_any(pb_ctx* c, const pb_ray* rays, uint64_t n, uint8_t* occ, int host, void* stream) {
+    return trace_entry(c, rays, n, occ, host, stream, true, false);
+}
+PB_API int pb_trace_closest_counted(pb_ctx* c, const pb_ray* rays, uint64_t n, pb_hit* hits, int host, void* stream) {
+    return trace_entry(c, rays, n, hits, host, stream, false, true);
+}
+PB_API int pb_trace_any_counted(pb_ctx* c, const pb_ray* rays, uint64_t n, uint8_t* occ, int host, void* stream) {
+    return trace_entry(c, rays, n, occ, host, stream, true, true);
+}
+
+PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba, float* albedo_rgb, float* normal_rgb, void* stream) {
+    if (!c) return PB_ERR_INVALID;
+    if (!c->committed) { c->err = "scene not committed"; return PB_ERR_NOT_COMMITTED; }
+    PB_REQUIRE(p && accum_sum_rgba, "null render params / accumulation buffer");
+    PB_REQUIRE(p->width && p->height, "empty film");
+    cudaSetDevice(c->device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    const size_t npx = (size_t)p->width * p->height;
+    if (!(p->flags & PB_RENDER_HOST_BUFFERS)) {
+        int rc = wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, s);
+        if (rc != PB_OK) return rc;
+        PB_CUDA_TRY(c, cudaStreamSynchronize(s));
+        return PB_OK;
+    }
+    float *d_sum = nullptr, *d_alb = nullptr, *d_nrm = nullptr;
+    PB_CUDA_TRY(c, cudaMalloc(&d_sum, npx * 16));
+    if (albedo_rgb) PB_CUDA_TRY(c, cudaMalloc(&d_alb, npx * 12));
+    if (normal_rgb) PB_CUDA_TRY(c, cudaMalloc(&d_nrm, npx * 12));
+    if (!(p->flags & PB_RENDER_CLEAR)) PB_CUDA_TRY(c, cudaMemcpyAsync(d_sum, accum_sum_rgba, npx * 16, cudaMemcpyHostToDevice, s));
+    int rc = wavefront_render(c, p, d_sum, d_alb, d_nrm, s);
+    if (rc == PB_OK) {
+        cudaError_t e = cudaMemcpyAsync(accum_sum_rgba, d_sum, npx * 16, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess && albedo_rgb) e = cudaMemcpyAsync(albedo_rgb, d_alb, npx * 12, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess && normal_rgb) e = cudaMemcpyAsync(normal_rgb, d_nrm, npx * 12, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { c->err = std::string("render (host buffers): ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
+    }
+    cudaFree(d_sum); cudaFree(d_alb); cudaFree(d_nrm);
+    return rc;
+}
+
+PB_API int pb_resolve(pb_ctx* c, const float* sum, float* frame, uint32_t n, int host, void* stream) {
+    if (!c) return PB_ERR_INVALID;
+    cudaSetDevice(c->device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    if (!host) {
+        int rc = resolve_frame(c, sum, frame, n, s);
+        if (rc != PB_OK) return rc;
+        PB_CUDA_TRY(c, cudaStreamSynchronize(s));
+        return PB_OK;
+    }
+    float *d_a = nullptr, *d_b = nullptr;
+    PB_CUDA_TRY(c, cudaMalloc(&d_a, (size_t)n * 16)); PB_CUDA_TRY(c, cudaMalloc(&d_b, (size_t)n * 16));
+    PB_CUDA_TRY(c, cudaMemcpyAsync(d_a, sum, (size_t)n * 16, cudaMemcpyHostToDevice, s));
+    int rc = resolve_frame(c, d_a, d_b, n, s);
+    if (rc == PB_OK) {
+        PB_CUDA_TRY(c, cudaMemcpyAsync(frame, d_b, (size_t)n * 16, cudaMemcpyDeviceToHost, s));
+        PB_CUDA_TRY(c, cudaStreamSynchronize(s));
+    }
+    cudaFree(d_a); cudaFree(d_b);
+    return rc;
+}
+
+PB_API int pb_get_stats(pb_ctx* c, pb_stats* out) {
+    if (!c || !out) return PB_ERR_INVALID;
+    *out = c->stats;
+    return PB_OK;
+}
+
+PB_API int pb_export_bvh(pb_ctx* c, void* nodes80, uint64_t* n_nodes, void* prims48, uint64_t* n_prims) {
+    if (!c) return PB_ERR_INVALID;
+    if (!c->committed) { c->err = "scene not committed"; return PB_ERR_NOT_COMMITTED; }
+    cudaSetDevice(c->device);
+    if (n_nodes) *n_nodes = c->n_nodes;
+    if (n_prims) *n_prims = c->n_prims;
+    if (nodes80 && c->n_nodes) PB_CUDA_TRY(c, cudaMemcpy(nodes80, c->d_nodes, (size_t)c->n_nodes * sizeof(Node8), cudaMemcpyDeviceToHost));
+    if (prims48 && c->n_prims) PB_CUDA_TRY(c, cudaMemcpy(prims48, c->d_prims, (size_t)c->n_prims * sizeof(PrimRec), cudaMemcpyDeviceToHost));
+    return PB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,93 @@
+// pb_internal.h — the context behind pb_ctx and declarations shared by the translation units.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/pupil_b200.h"
+#include "pb_types.h"
+#include "pb_traverse.cuh"
+
+namespace pb {
+
+struct HostObject {
+    bool sphere = false;
+    float M[12]{};
+    uint32_t flags = 0, material = 0;
+    bool is_emitter = false;
+    pb_texture area_radiance{};
+    uint32_t vert_offset = 0, n_vert = 0, index_offset = 0, n_tri = 0;
+    bool has_nrm = false, has_uv = false;
+};
+
+struct Wavefront;  // pb_wavefront.cu
+
+}  // namespace pb
+
+struct pb_ctx {
+    int device = 0;
+    std::string err;
+    cudaStream_t stream = nullptr;   // internal stream used when the caller passes none
+    bool in_scene = false, committed = false;
+
+    // ---- host copy of the scene (kept for pb_update_instance)
+    std::vector<pb_material> materials;
+    std::vector<pb::HostObject> objects;
+    std::vector<float> h_pos, h_nrm, h_uv;
+    std::vector<uint32_t> h_idx;
+    std::vector<std::vector<float>> bitmaps;   // owned copies of bitmap texels
+    pb_env env{};
+    pb::Camera cam{};
+
+    // ---- device scene
+    float* d_pos = nullptr; float* d_nrm = nullptr; float* d_uv = nullptr; uint32_t* d_idx = nullptr;
+    pb::ObjRec* d_objs = nullptr;
+    pb::MatRec* d_mats = nullptr;
+    pb::EmitRec* d_emit = nullptr;       // area emitters, then (optionally) the env emitter
+    float* d_emit_prefix = nullptr;      // running sums of select_probability (emitter.h:110-121)
+    float* d_env_tables = nullptr;
+    uint32_t n_area_emitters = 0;
+    bool has_env = false;
+    std::vector<pb::ObjRec> h_objs;
+    std::vector<cudaTextureObject_t> tex_objects;
+    std::vector<cudaArray_t> tex_arrays;
+
+    // ---- BVH
+    pb::Node8* d_nodes = nullptr;
+    pb::PrimRec* d_prims = nullptr;      // leaf order
+    uint32_t n_nodes = 0, n_prims = 0, bvh_levels = 0;
+    float delta = 0.f;
+    pb::V3 scene_lo{}, scene_hi{};
+
+    // ---- scratch
+    unsigned long long* d_counters = nullptr;   // [0] ray fetch cursor, [1..3] visit counters
+    pb::Wavefront* wf = nullptr;
+    int sm_count = 148;
+    pb_stats stats{};
+
+    pb::TraceScene trace_scene() const {
+        return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes};
+    }
+};
+
+#define PB_CUDA_TRY(ctx, call)                                                                       \
+    do {                                                                                             \
+        cudaError_t _e = (call);                                                                     \
+        if (_e != cudaSuccess) {                                                                     \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(_e);                         \
+            return PB_ERR_CUDA;                                                                      \
+        }                                                                                            \
+    } while (0)
+
+namespace pb {
+// pb_build.cu
+int build_bvh(pb_ctx* c, const PrimRec* d_prims_in, uint32_t n, cudaStream_t s);
+int make_world_prims(pb_ctx* c, PrimRec* d_out, cudaStream_t s);   // also computes scene box + delta
+// pb_trace.cu
+int trace_rays(pb_ctx* c, const pb_ray* d_rays, uint64_t n, pb_hit* d_hits, uint8_t* d_occ, bool any, bool counted, cudaStream_t s);
+// pb_wavefront.cu
+int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, cudaStream_t s);
+void wavefront_free(pb_ctx* c);
+int resolve_frame(pb_ctx* c, const float* d_sum, float* d_frame, uint32_t n, cudaStream_t s);
+}  // namespace pb

@@ -199,3 +199,143 @@ def cornell_box(ctx: capi.Context, width=256, height=256, variant="diffuse") -> 
     set_perspective_camera(ctx, 19.5, width, height, CORNELL_SENSOR)
     ctx.commit()
     return {"width": width, "height": height, "objects": objs, "materials": mats}
+
+
+# ------------------------------------------------------------------------------------------------
+# Procedural displaced mesh + spheres (configs C3/C4/C5)
+
+def _hash2(ix, iy, seed):
+    h = (ix.astype(np.uint64) * np.uint64(0x9E3779B1) + iy.astype(np.uint64) * np.uint64(0x85EBCA77) + np.uint64(seed) * np.uint64(0xC2B2AE3D)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(15)
+    h = (h * np.uint64(0x2C1B3C6D)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(12)
+    h = (h * np.uint64(0x297A2D39)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(15)
+    return (h & np.uint64(0xFFFFFF)).astype(np.float64) / float(1 << 24)
+
+
+def _value_noise(x, y, seed):
+    x0, y0 = np.floor(x), np.floor(y)
+    fx, fy = x - x0, y - y0
+    ix, iy = x0.astype(np.int64) & 0xFFFF, y0.astype(np.int64) & 0xFFFF
+    sx, sy = fx * fx * (3 - 2 * fx), fy * fy * (3 - 2 * fy)
+    a, b = _hash2(ix, iy, seed), _hash2(ix + 1, iy, seed)
+    c, d = _hash2(ix, iy + 1, seed), _hash2(ix + 1, iy + 1, seed)
+    return (a + (b - a) * sx) * (1 - sy) + (c + (d - c) * sx) * sy
+
+
+def height_field(x, z, seed=1234):
+    """4 octaves of value noise, amplitude 0.15 * 2^-o."""
+    h = np.zeros_like(x, dtype=np.float64)
+    for o in range(4):
+        f = 3.0 * (2 ** o)
+        h += 0.15 * 2.0 ** (-o) * _value_noise((x + 1.0) * f, (z + 1.0) * f, seed + o)
+    return h
+
+
+def displaced_mesh(n: int, seed: int = 1234):
+    """(n+1)^2 grid over [-1,1]^2 in XZ, 2 n^2 triangles; vertex normals from central differences,
+    uv = grid coordinates.  n = 707 -> 1.0 M, 2236 -> 10.0 M, 7071 -> 100.0 M triangles."""
+    g = np.linspace(-1.0, 1.0, n + 1)
+    X, Z = np.meshgrid(g, g, indexing="xy")
+    Y = height_field(X, Z, seed)
+    pos = np.stack([X, Y, Z], -1).reshape(-1, 3).astype(np.float32)
+    e = 2.0 / n
+    dx = (height_field(X + e, Z, seed) - height_field(X - e, Z, seed)) / (2 * e)
+    dz = (height_field(X, Z + e, seed) - height_field(X, Z - e, seed)) / (2 * e)
+    nrm = np.stack([-dx, np.ones_like(dx), -dz], -1)
+    nrm /= np.linalg.norm(nrm, axis=-1, keepdims=True)
+    nrm = nrm.reshape(-1, 3).astype(np.float32)
+    uv = np.stack([(X + 1) * 0.5, (Z + 1) * 0.5], -1).reshape(-1, 2).astype(np.float32)
+    i, j = np.meshgrid(np.arange(n, dtype=np.uint32), np.arange(n, dtype=np.uint32), indexing="xy")
+    v00 = (j * (n + 1) + i).reshape(-1)
+    v10, v01, v11 = v00 + 1, v00 + (n + 1), v00 + (n + 2)
+    idx = np.empty((2 * n * n, 3), np.uint32)
+    idx[0::2] = np.stack([v00, v01, v11], -1)   # counter-clockwise seen from +Y
+    idx[1::2] = np.stack([v00, v11, v10], -1)
+    return pos, nrm, uv, idx
+
+
+MESH_N = {"1M": 707, "10M": 2236, "100M": 7071}
+BENCH_CAMERA = dict(origin=(0.0, 1.2, 2.6), target=(0.0, 0.1, 0.0), up=(0.0, 1.0, 0.0), fov=45.0)
+
+
+def seven_materials(ctx):
+    """One material of each type (parameters as in data/static/material_test.xml)."""
+    M = capi.make_material
+    au = dict(eta=(0.200438, 0.924033, 1.10221), k=(3.91295, 2.45285, 2.14219))
+    return [
+        ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True, reflectance=(0.7, 0.7, 0.7))),
+        ctx.add_material(M(capi.MAT_DIELECTRIC, int_ior=1.5, ext_ior=1.0)),
+        ctx.add_material(M(capi.MAT_ROUGH_DIELECTRIC, int_ior=1.5, ext_ior=1.0, alpha=0.35)),
+        ctx.add_material(M(capi.MAT_CONDUCTOR, twosided=True, specular_reflectance=0.8, **au)),
+        ctx.add_material(M(capi.MAT_ROUGH_CONDUCTOR, twosided=True, alpha=0.35, specular_reflectance=0.8, **au)),
+        ctx.add_material(M(capi.MAT_PLASTIC, twosided=True, int_ior=1.5, ext_ior=1.0, reflectance=(0.65, 0.3, 0.2))),
+        ctx.add_material(M(capi.MAT_ROUGH_PLASTIC, twosided=True, int_ior=1.5, ext_ior=1.0, alpha=0.35, reflectance=(0.2, 0.4, 0.65))),
+    ]
+
+
+def bench_scene(ctx, mesh_n: int, n_spheres: int = 10000, width=1920, height=1080, patchwork=True, mesh=None):
+    """Displaced mesh (+ `n_spheres` spheres cycling the 7 materials) lit by one rectangle light at
+    y = 1.5 (radiance 17,12,4; 0.5 x 0.5).  With `patchwork` the mesh is split into 7 objects by
+    64x64-quad tiles (material = hash(tile) mod 7), otherwise it is one diffuse object (C3)."""
+    pos, nrm, uv, idx = mesh if mesh is not None else displaced_mesh(mesh_n)
+    ctx.scene_begin()
+    mats = seven_materials(ctx)
+    ident = np.eye(4, dtype=np.float32)
+    if patchwork:
+        quad = np.arange(mesh_n * mesh_n, dtype=np.int64)
+        ti, tj = (quad % mesh_n) // 64, (quad // mesh_n) // 64
+        m_of_quad = ((ti * 73856093) ^ (tj * 19349663)) % 7
+        m_of_tri = np.repeat(m_of_quad, 2)
+        for k in range(7):
+            sel = idx[m_of_tri == k]
+            if len(sel):
+                ctx.add_trimesh(pos, nrm, uv, sel, ident, 0, mats[k])
+    else:
+        ctx.add_trimesh(pos, nrm, uv, idx, ident, 0, mats[0])
+    rng = np.random.RandomState(42)
+    ctr = np.stack([rng.uniform(-1, 1, n_spheres), rng.uniform(0.05, 0.6, n_spheres), rng.uniform(-1, 1, n_spheres)], -1)
+    rad = rng.uniform(0.005, 0.02, n_spheres)
+    for s in range(n_spheres):
+        add_sphere(ctx, ctr[s], float(rad[s]), mats[s % 7])
+    light_black = ctx.add_material(capi.make_material(capi.MAT_DIFFUSE, twosided=True, reflectance=(0, 0, 0)))
+    lm = translate(0, 1.5, 0) @ rotate(1, 0, 0, 90) @ scale(0.25, 0.25, 1)
+    add_rectangle(ctx, lm, light_black, 0, capi.rgb_texture(17, 12, 4))
+    cam = BENCH_CAMERA
+    to_world = lookat_to_world(cam["origin"], cam["target"], cam["up"])  # <lookat> flip; the sensor flips it again (SURVEY 3.3)
+    set_perspective_camera(ctx, cam["fov"], width, height, to_world)
+    ctx.commit()
+    return dict(width=width, height=height, n_tris=len(idx), n_spheres=n_spheres)
+
+
+def camera_rays(s2c, c2w, width, height, seed=0, pixels=None):
+    """Primary rays exactly as __raygen__main builds them (main.cu:53-75), vectorised in fp32 numpy;
+    jitter from the reference RNG Init(4, pixel, seed)."""
+    px = np.arange(width * height, dtype=np.uint32) if pixels is None else np.asarray(pixels, np.uint32)
+    v0, v1, s0 = px.copy(), np.full_like(px, seed), np.uint32(0)
+    with np.errstate(over="ignore"):
+        for _ in range(4):
+            s0 = np.uint32(s0 + np.uint32(0x9E3779B9))
+            v0 = v0 + ((((v1 << np.uint32(4)) + np.uint32(0xA341316C)) ^ (v1 + s0) ^ ((v1 >> np.uint32(5)) + np.uint32(0xC8013EA4))))
+            v1 = v1 + ((((v0 << np.uint32(4)) + np.uint32(0xAD90777D)) ^ (v0 + s0) ^ ((v0 >> np.uint32(5)) + np.uint32(0x7E95761E))))
+        st = v0
+        st = st * np.uint32(1664525) + np.uint32(1013904223)
+        jx = (st & np.uint32(0xFFFFFF)).astype(np.float32) / np.float32(1 << 24)
+        st = st * np.uint32(1664525) + np.uint32(1013904223)
+        jy = (st & np.uint32(0xFFFFFF)).astype(np.float32) / np.float32(1 << 24)
+    x, y = (px % np.uint32(width)).astype(np.float32), (px // np.uint32(width)).astype(np.float32)
+    sx, sy = (x + jx) / np.float32(width), (y + jy) / np.float32(height)
+    s2c, c2w = np.asarray(s2c, np.float32).reshape(4, 4), np.asarray(c2w, np.float32).reshape(4, 4)
+    d = [(s2c[r, 0] * sx + s2c[r, 1] * sy) + s2c[r, 2] * np.float32(0) + s2c[r, 3] * np.float32(1) for r in range(4)]
+    inv = np.float32(1) / d[3]
+    d = [d[0] * inv, d[1] * inv, d[2] * inv]
+    inv = np.float32(1) / np.sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2])
+    d = [v * inv for v in d]
+    w = [c2w[r, 0] * d[0] + c2w[r, 1] * d[1] + c2w[r, 2] * d[2] for r in range(3)]
+    inv = np.float32(1) / np.sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2])
+    rays = np.zeros(len(px), capi.RAY_DTYPE)
+    rays["ox"], rays["oy"], rays["oz"] = c2w[0, 3], c2w[1, 3], c2w[2, 3]
+    rays["dx"], rays["dy"], rays["dz"] = w[0] * inv, w[1] * inv, w[2] * inv
+    rays["tmin"], rays["tmax"] = 1e-3, 1e16
+    return rays
