@@ -29,7 +29,7 @@ struct TraceScene {
     uint32_t n_nodes;
 };
 
-struct Hit { float t, u, v; uint32_t prim; };
+struct Hit { float t, u, v; uint32_t prim; uint32_t obj; };
 struct TraceCounters { unsigned long long nodes, tris, spheres; };
 
 #if defined(__CUDA_ARCH__)
@@ -114,7 +114,7 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
 
 template<bool ANY, bool COUNT>
 PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hit& best, LaneStack& st, TraceCounters* cnt) {
-    best.t = tmax; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu;
+    best.t = tmax; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu; best.obj = 0xFFFFFFFFu;
     if (sc.n_nodes == 0) return;
     const RayPre pre = ray_pre(o, d);
     const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
@@ -149,8 +149,8 @@ PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hi
             float t, u, v;
             if (prim_accept(r, sc.objs, o, d, pre, tmin, tmax, sc.delta, t, u, v)) {
                 const uint32_t id = f2u(r.a.w);
-                if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; return; }
-                if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; }
+                if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); return; }
+                if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); }
             }
         }
         if (!(G.y & 0xff000000u)) {

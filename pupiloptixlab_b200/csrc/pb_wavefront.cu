@@ -1,14 +1,445 @@
-// pb_wavefront.cu — wavefront pt+MIS integrator (placeholder until the kernels land in this file).
+// pb_wavefront.cu — wavefront pt+MIS integrator.  Replaces the __raygen__main megakernel and its
+// miss / closest-hit programs (example/path_tracer/main.cu:36-233) and the per-frame launch loop of
+// PTPass::OnRun (example/path_tracer/pt_pass.cpp:39-57).
+//
+// One WAVE renders K consecutive frames (samples) of every pixel at once: path slot = k * n_pixels
+// + pixel.  Per bounce:   extend (closest hit, bins paths by material)  ->  shade<MAT> x 7 + miss
+// (emission/MIS at the hit, Russian roulette, NEE sample -> shadow queue, BSDF sample -> next ray)
+// ->  connect (any hit; adds the NEE contribution).  After max_depth bounces `accumulate` adds the K
+// radiances of each pixel to the sum buffer in frame order (deterministic, no atomics on pixels).
+// Path state is SoA in HBM (float4 per field), queues are compacted with warp ballots + one atomic
+// per warp, every kernel is persistent over a device-side counter so a wave needs no host sync.
+#include <algorithm>
+
+#include "pb_bsdf.cuh"
+#include "pb_emitter.cuh"
+#include "pb_geom.cuh"
 #include "pb_internal.h"
 
 namespace pb {
 
+constexpr int kWfThreads = 128;
+enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_COUNT = 16 };
+enum : uint32_t { F_DEPTH_MASK = 0xffu, F_DELTA = 0x100u };
+
+struct WfState {
+    // per path slot
+    float4* ray;        // 2 per slot: (o.xyz, tmin) (d.xyz, tmax)
+    float4* hit;        // (t, u, v, prim bits)
+    uint32_t* hit_obj;
+    float4* thr;        // throughput.xyz, pdf of the BSDF sample that produced the current ray
+    float4* rad;        // radiance.xyz, rng state bits
+    uint32_t* flags;    // depth | F_DELTA
+    // queues
+    uint32_t* q_ext[2];
+    uint32_t* q_mat;    // 8 queues of `cap` entries: 0 = miss, 1..7 = material type
+    float4* sh_ray;     // 2 per shadow entry
+    float4* sh_con;     // contribution.xyz, slot bits
+    uint32_t* cnt;      // C_* counters
+    unsigned long long* totals;  // [0] closest rays, [1] any rays
+    uint32_t cap;
+};
+
+struct Wavefront {
+    WfState st{};
+    uint32_t cap = 0;
+    void* block = nullptr;
+};
+
+struct WfScene {
+    TraceScene ts;
+    SceneGeom geom;
+    const MatRec* mats;
+    EmitterTable em;
+    Camera cam;
+    uint32_t width, height, n_px, max_depth;
+    uint32_t first_sample, stride;
+};
+
+// ---- warp-aggregated queue append: every lane of the warp must call ---------------------------------
+__device__ __forceinline__ uint32_t warp_append(uint32_t* counter, bool pred) {
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, pred);
+    if (m == 0u) return 0u;
+    const unsigned lane = threadIdx.x & 31u;
+    uint32_t base = 0;
+    if (lane == (unsigned)(__ffs(m) - 1)) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+    return base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+
+// ---- stage 0: per-iteration bookkeeping (single thread) --------------------------------------------
+__global__ void k_prepare(WfState s, int cur, uint32_t set_cur_count, int set) {
+    if (set) s.cnt[cur ? C_EXT_B : C_EXT_A] = set_cur_count;
+    s.totals[0] += s.cnt[cur ? C_EXT_B : C_EXT_A];
+    s.cnt[cur ? C_EXT_A : C_EXT_B] = 0;            // next extend queue
+    s.cnt[C_SHADOW] = 0;
+    for (int k = 0; k < 8; ++k) s.cnt[C_MAT0 + k] = 0;
+    s.cnt[C_CUR_EXT] = 0; s.cnt[C_CUR_CON] = 0;
+}
+__global__ void k_after_shade(WfState s) { s.totals[1] += s.cnt[C_SHADOW]; }
+
+// ---- generate: camera rays of K frames (main.cu:37-75) ----------------------------------------------
+__global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_t wave_first_k, uint32_t n_paths) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_paths) return;
+    const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
+    const uint32_t x = pixel % sc.width, y = pixel / sc.width;
+    Rng rng;
+    rng.init(pixel, sc.first_sample + (wave_first_k + k) * sc.stride);
+    const float jx = rng.next(), jy = rng.next();
+    const float sx = (static_cast<float>(x) + jx) / static_cast<float>(sc.width);
+    const float sy = (static_cast<float>(y) + jy) / static_cast<float>(sc.height);
+    const V4 pof = {sx, sy, 0.f, 1.f};
+    const float* m = sc.cam.s2c;
+    V4 d = {dot(V4{m[0], m[1], m[2], m[3]}, pof), dot(V4{m[4], m[5], m[6], m[7]}, pof), dot(V4{m[8], m[9], m[10], m[11]}, pof),
+            dot(V4{m[12], m[13], m[14], m[15]}, pof)};
+    { const float inv = 1.0f / d.w; d.x *= inv; d.y *= inv; d.z *= inv; d.w *= inv; }
+    d.w = 0.f;
+    d = normalize(d);
+    const float* w = sc.cam.c2w;
+    const V3 dir = normalize(v3(dot(V4{w[0], w[1], w[2], w[3]}, d), dot(V4{w[4], w[5], w[6], w[7]}, d), dot(V4{w[8], w[9], w[10], w[11]}, d)));
+    s.ray[2 * slot] = make_float4(w[3], w[7], w[11], 0.001f);
+    s.ray[2 * slot + 1] = make_float4(dir.x, dir.y, dir.z, 1e16f);
+    s.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+    s.rad[slot] = make_float4(0.f, 0.f, 0.f, __uint_as_float(rng.s));
+    s.flags[slot] = 0u;
+    s.q_ext[0][slot] = slot;
+}
+
+// ---- extend: closest hit for every queued path, then bin by material --------------------------------
+__global__ void __launch_bounds__(kWfThreads) k_extend(WfState s, WfScene sc, int cur) {
+    __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
+    LaneStack st;
+    st.init(s_stack + threadIdx.x, kWfThreads);
+    const uint32_t n = s.cnt[cur ? C_EXT_B : C_EXT_A];
+    const uint32_t* q = s.q_ext[cur];
+    const unsigned lane = threadIdx.x & 31u;
+    while (true) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&s.cnt[C_CUR_EXT], 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const uint32_t i = base + lane;
+        uint32_t bin = 8u, slot = 0u;
+        if (i < n) {
+            slot = q[i];
+            const float4 a = s.ray[2 * slot], b = s.ray[2 * slot + 1];
+            Hit h;
+            traverse<false, false>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, nullptr);
+            s.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+            s.hit_obj[slot] = h.obj;
+            bin = h.prim == 0xFFFFFFFFu ? 0u : sc.mats[sc.geom.objs[h.obj].material].type;
+        }
+#pragma unroll
+        for (uint32_t b = 0; b < 8u; ++b) {   // warp-aggregated append, one queue at a time
+            const uint32_t pos = warp_append(&s.cnt[C_MAT0 + b], bin == b);
+            if (bin == b) s.q_mat[(size_t)b * s.cap + pos] = slot;
+        }
+    }
+}
+
+// ---- connect: any hit for the shadow queue; unoccluded contributions go to the path radiance --------
+__global__ void __launch_bounds__(kWfThreads) k_connect(WfState s, WfScene sc) {
+    __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
+    LaneStack st;
+    st.init(s_stack + threadIdx.x, kWfThreads);
+    const uint32_t n = s.cnt[C_SHADOW];
+    const unsigned lane = threadIdx.x & 31u;
+    while (true) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&s.cnt[C_CUR_CON], 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const uint32_t i = base + lane;
+        if (i < n) {
+            const float4 a = s.sh_ray[2 * i], b = s.sh_ray[2 * i + 1];
+            Hit h;
+            traverse<true, false>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, nullptr);
+            if (h.prim == 0xFFFFFFFFu) {
+                const float4 c = s.sh_con[i];
+                const uint32_t slot = __float_as_uint(c.w);
+                float4 r = s.rad[slot];
+                r.x += c.x; r.y += c.y; r.z += c.z;   // one shadow ray per path per bounce: no race
+                s.rad[slot] = r;
+            }
+        }
+    }
+}
+
+
+// ---- shade<MAT>: one path vertex.  Follows main.cu:84-183 line by line -----------------------------------
+template<int MAT>
+__global__ void __launch_bounds__(kWfThreads) k_shade(WfState s, WfScene sc, int cur, uint32_t k_aov, float* albedo, float* normal) {
+    const uint32_t n = s.cnt[C_MAT0 + MAT];
+    const uint32_t* q = s.q_mat + (size_t)MAT * s.cap;
+    uint32_t* qnext = s.q_ext[cur ^ 1];
+    uint32_t* next_count = &s.cnt[cur ? C_EXT_A : C_EXT_B];
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t base = warp * 32u; base < n; base += n_warps * 32u) {
+        const uint32_t i = base + lane;
+        bool push_ray = false, push_shadow = false;
+        uint32_t slot = 0;
+        V3 sh_o = v3(0.f), sh_d = v3(0.f), contrib = v3(0.f);
+        float sh_tmax = 0.f;
+        if (i < n) {
+            slot = q[i];
+            const float4 ro4 = s.ray[2 * slot], rd4 = s.ray[2 * slot + 1], h4 = s.hit[slot];
+            const V3 ray_o = {ro4.x, ro4.y, ro4.z}, ray_d = {rd4.x, rd4.y, rd4.z};
+            const uint32_t prim = __float_as_uint(h4.w);
+            const ObjRec& o = sc.geom.objs[s.hit_obj[slot]];
+            const MatRec& m = sc.mats[o.material];
+            const LocalGeo geo = hit_geometry(sc.geom, o, prim, h4.x, h4.y, h4.z, ray_o, ray_d, m.twosided != 0u);
+            const BsdfLocal bsdf = bsdf_local<MAT>(m, geo.texcoord);
+            const int emitter_index = o.emitter_offset >= 0 ? o.emitter_offset + (int)(prim - o.prim_offset) : -1;
+            const float4 t4 = s.thr[slot];
+            float4 r4 = s.rad[slot];
+            V3 throughput = {t4.x, t4.y, t4.z}, radiance = {r4.x, r4.y, r4.z};
+            Rng rng; rng.s = __float_as_uint(r4.w);
+            const uint32_t fl = s.flags[slot];
+            int depth = (int)(fl & F_DEPTH_MASK);
+            if (depth == 0) {  // primary hit: main.cu:87-101
+                if (emitter_index >= 0) radiance += emitter_radiance(sc.em.rec[emitter_index], geo.texcoord);
+                const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
+                if (k == k_aov) {
+                    if (albedo) { const V3 a = bsdf_albedo<MAT>(bsdf); albedo[3 * pixel] = a.x; albedo[3 * pixel + 1] = a.y; albedo[3 * pixel + 2] = a.z; }
+                    if (normal) { normal[3 * pixel] = geo.normal.x; normal[3 * pixel + 1] = geo.normal.y; normal[3 * pixel + 2] = geo.normal.z; }
+                }
+                (void)rng.next();  // test[pixel] = rng.Next(), main.cu:101
+            } else if (emitter_index >= 0) {  // emitter hit by the BSDF sample: main.cu:171-182
+                const EmitRec& e = sc.em.rec[emitter_index];
+                EmitEval ev;
+                emitter_eval(e, ev, geo.position, geo.normal, geo.texcoord, ray_o);
+                if (!is_zero(ev.pdf)) {
+                    const float mis = (fl & F_DELTA) ? 1.f : mis_weight(t4.w, ev.pdf * e.select_probability);
+                    radiance += throughput * ev.radiance * mis;
+                }
+            }
+            // ---- loop body, main.cu:103-163
+            bool alive = true;
+            ++depth;
+            if (depth >= (int)sc.max_depth) alive = false;
+            if (alive) {
+                const float rr = depth > 2 ? 0.95 : 1.0;
+                if (rng.next() > rr) alive = false;
+                else throughput /= rr;
+            }
+            if (alive) {
+                {  // direct light sampling, main.cu:113-140
+                    const uint32_t ei = select_emitter(sc.em, rng.next());
+                    const EmitRec& e = sc.em.rec[ei];
+                    const float x1 = rng.next(), x2 = rng.next();
+                    EmitterSample es;
+                    emitter_sample_direct(e, es, geo.position, geo.normal, x1, x2);
+                    if (es.valid_distance) {
+                        BsdfRec er;
+                        er.wi = to_local(es.wi, geo.normal);
+                        er.wo = to_local(-ray_d, geo.normal);
+                        bsdf_eval<MAT>(bsdf, er);
+                        if (!is_zero(er.f * es.pdf)) {
+                            const float NoL = dot(geo.normal, es.wi);
+                            if (NoL > 0.f) {
+                                const float mis = mis_weight(es.pdf, er.pdf);
+                                const float pdf_e = es.pdf * e.select_probability;
+                                contrib = throughput * es.radiance * er.f * NoL * mis / pdf_e;
+                                sh_o = geo.position; sh_d = es.wi; sh_tmax = es.distance - 0.001f;
+                                push_shadow = true;
+                            }
+                        }
+                    }
+                }
+                {  // bsdf sampling, main.cu:141-163
+                    BsdfRec br;
+                    br.wo = to_local(-ray_d, geo.normal);
+                    bsdf_sample<MAT>(bsdf, br, rng);
+                    if (is_zero(br.f * fabsf(br.wi.z)) || is_zero(br.pdf)) {
+                        alive = false;
+                    } else {
+                        throughput *= br.f * fabsf(br.wi.z) / br.pdf;
+                        const V3 nd = to_world(br.wi, geo.normal);
+                        s.ray[2 * slot] = make_float4(geo.position.x, geo.position.y, geo.position.z, 0.001f);
+                        s.ray[2 * slot + 1] = make_float4(nd.x, nd.y, nd.z, 1e16f);
+                        s.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, br.pdf);
+                        s.flags[slot] = (uint32_t)depth | ((br.lobe & LOBE_DELTA) ? F_DELTA : 0u);
+                        push_ray = true;
+                    }
+                }
+            }
+            s.rad[slot] = make_float4(radiance.x, radiance.y, radiance.z, __uint_as_float(rng.s));
+        }
+        const uint32_t pr = warp_append(next_count, push_ray);
+        if (push_ray) qnext[pr] = slot;
+        const uint32_t ps = warp_append(&s.cnt[C_SHADOW], push_shadow);
+        if (push_shadow) {
+            s.sh_ray[2 * ps] = make_float4(sh_o.x, sh_o.y, sh_o.z, 0.001f);
+            s.sh_ray[2 * ps + 1] = make_float4(sh_d.x, sh_d.y, sh_d.z, sh_tmax);
+            s.sh_con[ps] = make_float4(contrib.x, contrib.y, contrib.z, __uint_as_float(slot));
+        }
+    }
+}
+
+// ---- miss: __miss__default (main.cu:196-212) + main.cu:165-169,185 ----------------------------------------
+__global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_aov, float* albedo, float* normal) {
+    const uint32_t n = s.cnt[C_MAT0];
+    const EmitRec& env = sc.em.rec[sc.em.n_area];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = s.q_mat[i];
+        const uint32_t fl = s.flags[slot];
+        const bool primary = (fl & F_DEPTH_MASK) == 0u;
+        if (primary) {
+            const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
+            if (k == k_aov) {
+                if (albedo) { albedo[3 * pixel] = 0.f; albedo[3 * pixel + 1] = 0.f; albedo[3 * pixel + 2] = 0.f; }
+                if (normal) { normal[3 * pixel] = 0.f; normal[3 * pixel + 1] = 0.f; normal[3 * pixel + 2] = 0.f; }
+            }
+        }
+        if (env.type == EM_NONE) continue;
+        const float4 ro4 = s.ray[2 * slot], rd4 = s.ray[2 * slot + 1];
+        const V3 ray_o = {ro4.x, ro4.y, ro4.z}, rd = normalize(v3(rd4.x, rd4.y, rd4.z));
+        EmitEval ev;
+        emitter_eval(env, ev, ray_o + rd, v3(0.f), v2(0.f, 0.f), ray_o);
+        V3 env_radiance = ev.radiance;
+        float4 r4 = s.rad[slot];
+        if (!primary) {
+            const float4 t4 = s.thr[slot];
+            const float mis = mis_weight(t4.w, ev.pdf);
+            env_radiance *= v3(t4.x, t4.y, t4.z) * mis;
+        }
+        r4.x += env_radiance.x; r4.y += env_radiance.y; r4.z += env_radiance.z;
+        s.rad[slot] = r4;
+    }
+}
+
+// ---- accumulate: frame-ordered sum of the K radiances of each pixel (main.cu:187-193 as sum/count) ----------
+__global__ void __launch_bounds__(256) k_accumulate(WfState s, float4* sum, uint32_t n_px, uint32_t k_count) {
+    const uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pixel >= n_px) return;
+    float4 a = sum[pixel];
+    for (uint32_t k = 0; k < k_count; ++k) {
+        const float4 r = s.rad[(size_t)k * n_px + pixel];
+        a.x += r.x; a.y += r.y; a.z += r.z; a.w += 1.f;
+    }
+    sum[pixel] = a;
+}
+
 __global__ void k_resolve(const float4* __restrict__ sum, float4* __restrict__ frame, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const float4 s = sum[i];
-    const float inv = s.w > 0.f ? 1.0f / s.w : 0.f;   // mean of the frames added so far (main.cu:187-193)
-    frame[i] = make_float4(s.x * inv, s.y * inv, s.z * inv, 1.f);
+    const float4 v = sum[i];
+    const float inv = v.w > 0.f ? 1.0f / v.w : 0.f;   // mean of the frames added so far (main.cu:187-193)
+    frame[i] = make_float4(v.x * inv, v.y * inv, v.z * inv, 1.f);
+}
+
+
+// ---- host orchestration -------------------------------------------------------------------------------------
+static uint32_t wave_path_target() {
+    const char* e = getenv("PB_WAVE_PATHS");
+    long v = e ? atol(e) : 0;
+    return v > 0 ? (uint32_t)v : (8u << 20);
+}
+
+void wavefront_free(pb_ctx* c) {
+    if (!c->wf) return;
+    cudaFree(c->wf->block);
+    delete c->wf;
+    c->wf = nullptr;
+}
+
+static int wavefront_reserve(pb_ctx* c, uint32_t cap) {
+    if (c->wf && c->wf->cap >= cap) return PB_OK;
+    wavefront_free(c);
+    c->wf = new Wavefront();
+    auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t n = cap;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += al(bytes); return o; };
+    const size_t o_ray = take(n * 32), o_hit = take(n * 16), o_obj = take(n * 4), o_thr = take(n * 16), o_rad = take(n * 16),
+                 o_flags = take(n * 4), o_q0 = take(n * 4), o_q1 = take(n * 4), o_qm = take(n * 4 * 8), o_shr = take(n * 32),
+                 o_shc = take(n * 16), o_cnt = take(C_COUNT * 4), o_tot = take(16);
+    PB_CUDA_TRY(c, cudaMalloc(&c->wf->block, off));
+    char* b = static_cast<char*>(c->wf->block);
+    WfState& s = c->wf->st;
+    s.ray = (float4*)(b + o_ray); s.hit = (float4*)(b + o_hit); s.hit_obj = (uint32_t*)(b + o_obj);
+    s.thr = (float4*)(b + o_thr); s.rad = (float4*)(b + o_rad); s.flags = (uint32_t*)(b + o_flags);
+    s.q_ext[0] = (uint32_t*)(b + o_q0); s.q_ext[1] = (uint32_t*)(b + o_q1); s.q_mat = (uint32_t*)(b + o_qm);
+    s.sh_ray = (float4*)(b + o_shr); s.sh_con = (float4*)(b + o_shc);
+    s.cnt = (uint32_t*)(b + o_cnt); s.totals = (unsigned long long*)(b + o_tot);
+    s.cap = cap;
+    c->wf->cap = cap;
+    return PB_OK;
+}
+
+template<int MAT>
+static void launch_shade(const WfState& st, const WfScene& sc, int cur, uint32_t k_aov, float* alb, float* nrm, unsigned grid, cudaStream_t s) {
+    k_shade<MAT><<<grid, kWfThreads, 0, s>>>(st, sc, cur, k_aov, alb, nrm);
+}
+
+int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, cudaStream_t s) {
+    const uint32_t n_px = p->width * p->height;
+    if ((uint64_t)p->width * p->height > (1ull << 30)) { c->err = "film too large"; return PB_ERR_LIMIT; }
+    if (p->flags & PB_RENDER_CLEAR) PB_CUDA_TRY(c, cudaMemsetAsync(d_sum, 0, (size_t)n_px * 16, s));
+    if (p->sample_count == 0) return PB_OK;
+    uint32_t K = std::max<uint32_t>(1u, wave_path_target() / n_px);
+    K = std::min(K, p->sample_count);
+    if ((uint64_t)K * n_px > 0x7fffffffull) { c->err = "wave too large"; return PB_ERR_LIMIT; }
+    int rc = wavefront_reserve(c, K * n_px);
+    if (rc != PB_OK) return rc;
+    const WfState& st = c->wf->st;
+    WfScene sc{};
+    sc.ts = c->trace_scene();
+    sc.geom = SceneGeom{c->d_pos, c->d_nrm, c->d_uv, c->d_idx, c->d_objs, (uint32_t)c->h_objs.size(), c->n_prims};
+    sc.mats = c->d_mats;
+    sc.em = EmitterTable{c->d_emit, c->d_emit_prefix, c->n_area_emitters};
+    sc.cam = c->cam;
+    sc.width = p->width; sc.height = p->height; sc.n_px = n_px; sc.max_depth = p->max_depth;
+    sc.first_sample = p->first_sample; sc.stride = p->sample_stride ? p->sample_stride : 1u;
+
+    cudaEvent_t e0, e1;
+    PB_CUDA_TRY(c, cudaEventCreate(&e0)); PB_CUDA_TRY(c, cudaEventCreate(&e1));
+    PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 16, s));
+    cudaEventRecord(e0, s);
+    const unsigned g_trace = (unsigned)c->sm_count * 8u, g_shade = (unsigned)c->sm_count * 8u;
+    uint32_t launches = 0;
+    for (uint32_t k0 = 0; k0 < p->sample_count; k0 += K) {
+        const uint32_t kw = std::min(K, p->sample_count - k0);
+        const uint32_t n_paths = kw * n_px;
+        const bool last_wave = k0 + kw >= p->sample_count;
+        const uint32_t k_aov = last_wave ? kw - 1 : 0xFFFFFFFFu;   // AOVs of the last frame (main.cu:94-99)
+        k_generate<<<(n_paths + 255) / 256, 256, 0, s>>>(st, sc, k0, n_paths);
+        ++launches;
+        int cur = 0;
+        for (uint32_t b = 0; b < std::max(1u, p->max_depth); ++b) {
+            k_prepare<<<1, 1, 0, s>>>(st, cur, n_paths, b == 0 ? 1 : 0);
+            k_extend<<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
+            k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, d_albedo, d_normal);
+            launch_shade<1>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+            launch_shade<2>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+            launch_shade<3>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+            launch_shade<4>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+            launch_shade<5>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+            launch_shade<6>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+            launch_shade<7>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+            k_after_shade<<<1, 1, 0, s>>>(st);
+            k_connect<<<g_trace, kWfThreads, 0, s>>>(st, sc);
+            launches += 12;
+            cur ^= 1;
+        }
+        k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), n_px, kw);
+        ++launches;
+    }
+    cudaEventRecord(e1, s);
+    unsigned long long tot[2];
+    PB_CUDA_TRY(c, cudaMemcpyAsync(tot, st.totals, 16, cudaMemcpyDeviceToHost, s));
+    PB_CUDA_TRY(c, cudaStreamSynchronize(s));
+    PB_CUDA_TRY(c, cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    c->stats.last_render_ms = ms;
+    c->stats.rays_closest = tot[0]; c->stats.rays_any = tot[1];
+    c->stats.samples = (uint64_t)n_px * p->sample_count;
+    c->stats.kernel_launches = launches;
+    return PB_OK;
 }
 
 int resolve_frame(pb_ctx* c, const float* d_sum, float* d_frame, uint32_t n, cudaStream_t s) {
@@ -16,13 +447,6 @@ int resolve_frame(pb_ctx* c, const float* d_sum, float* d_frame, uint32_t n, cud
     k_resolve<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float4*>(d_sum), reinterpret_cast<float4*>(d_frame), n);
     PB_CUDA_TRY(c, cudaGetLastError());
     return PB_OK;
-}
-
-void wavefront_free(pb_ctx*) {}
-
-int wavefront_render(pb_ctx* c, const pb_render_params*, float*, float*, float*, cudaStream_t) {
-    c->err = "wavefront integrator not built into this library yet";
-    return PB_ERR_INVALID;
 }
 
 }  // namespace pb
