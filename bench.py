@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py — the headline measurement: Msamples/s (and Mrays/s) of the pt+MIS path at 1080p on the
+procedural 10 M-triangle displaced mesh + 10 k spheres scene (BASELINE.json configs[3], "C4"),
+depth 16, on N B200s of one box.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          the CUDA product (libpupil_b200.so)
+  python bench.py --impl reference ...                         the reference integrator's own header
+                                                               code on the host cores (oracle/_ref)
+
+One STEP = `--spp-per-step` (default 32) consecutive frames (= samples per pixel) of the whole
+1920x1080 film through pb_render; the default 8 timed steps are the config's 256 spp.  With N GPUs
+rank r renders the frames  s = r (mod N)  (same seeds as 1 GPU) and every step ends with
+an NCCL reduce of the fp32 sum buffer to rank 0 inside the timed region ("weak": per-GPU work fixed).
+
+Printed JSON (one line, rank 0): value = whole-job Msamples/s with the scene/BVH resident in HBM and
+device output buffers; e2e = the same through the C ABI with HOST (pinned) accumulation buffers —
+host->device and device->host copies inside the timed call; roofline = the closest-hit traversal
+kernel (k_extend) against the measured HBM copy bandwidth, algorithmic bytes per ray as defined in
+SURVEY 8(d) / DESIGN.md; cpu_baseline = the test oracle (reference headers on the host cores) on a
+bounded sample of the same workload.  oracle/ is only ever executed here for those two legs.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WIDTH, HEIGHT, MAX_DEPTH, N_SPHERES = 1920, 1080, 16, 10000
+WORKLOAD = "C4: procedural 10M-triangle displaced mesh + 10k spheres, 7-material patchwork, 1920x1080, depth 16, pt+MIS"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def build_scene(ctx, mesh_tag: str, mesh=None):
+    from pupiloptixlab_b200 import scenes
+    n = scenes.MESH_N[mesh_tag]
+    t0 = time.time()
+    mesh = mesh if mesh is not None else scenes.displaced_mesh(n)
+    t1 = time.time()
+    info = scenes.bench_scene(ctx, n, N_SPHERES, WIDTH, HEIGHT, patchwork=True, mesh=mesh)
+    info.update(mesh_s=t1 - t0, commit_s=time.time() - t1)
+    return info, mesh
+
+
+# --------------------------------------------------------------------------------------------------
+def cpu_leg(mesh_tag, mesh, seconds_target, steps, warmup, want_line):
+    """The reference integrator's header code on the host cores (oracle/_ref), bounded sample."""
+    from oracle import pyoracle
+    api = pyoracle.load()
+    o = pyoracle.OracleContext(api)
+    kind = "port"
+    if o.has_reference():
+        o.set_backend(1)
+        kind = "reference"
+    cores = int(api._max_threads())
+    info, mesh = build_scene(o, mesh_tag, mesh)
+    # probe, then the largest film (same camera, same scene) whose 1-spp frame fits the time budget
+    t0 = time.time(); o.render(240, 135, MAX_DEPTH, 0, 1, want_aov=False); probe = 240 * 135 / (time.time() - t0)
+    film = (240, 135)
+    for w, h in ((1920, 1080), (960, 540), (480, 270)):
+        if w * h / probe <= seconds_target:
+            film = (w, h)
+            break
+    w, h = film
+    rates, rays = [], 0
+    for i in range(warmup + steps):
+        t0 = time.time()
+        o.render(w, h, MAX_DEPTH, i, 1, want_aov=False)
+        dt = time.time() - t0
+        if i >= warmup:
+            st = o.stats()
+            rates.append(dt); rays += st["rays_closest"] + st["rays_any"]
+    total = sum(rates)
+    msps = w * h * steps / total / 1e6
+    sample = f"{steps} x 1 spp of the same scene/camera on a {w}x{h} film, depth {MAX_DEPTH} ({w * h * steps} samples, {total:.1f} s)"
+    base = {"value": msps, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": sample,
+            "mrays_per_s": rays / total / 1e6}
+    return base, total / steps * 1e3, info
+
+
+def reference_main(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    base, ms_per_step, info = cpu_leg(args.mesh, None, 8.0, args.steps, args.warmup, True)
+    line = {"impl": "reference", "metric": "Msamples/s at 1080p pt+MIS", "value": base["value"], "unit": "Msamples/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "mesh": args.mesh, "n_tris": info["n_tris"], "n_spheres": info["n_spheres"]},
+            "mrays_per_s": base["mrays_per_s"], "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------------
+def product_main(args):
+    import torch
+    import torch.distributed as dist
+    from pupiloptixlab_b200 import capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the host baseline)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    N = world
+    api = capi.load()
+    g = capi.Context(api, local)
+    info, mesh = build_scene(g, args.mesh)
+    st0 = g.stats()
+    if rank == 0:
+        log(f"[bench] scene: {info['n_tris']} tris + {info['n_spheres']} spheres, nodes={st0['n_nodes']}, "
+            f"bvh levels={st0['bvh_depth']}, build {st0['build_ms']:.0f} ms (host prep + device build), mesh gen {info['mesh_s']:.1f}s")
+
+    n_px = WIDTH * HEIGHT
+    S = args.spp_per_step
+    dev = torch.device("cuda", local)
+    d_sum = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32, device=dev)
+    d_total = torch.zeros_like(d_sum)
+    stream = torch.cuda.Stream(dev)      # everything (kernels, copies, NCCL) is ordered on this stream
+    torch.cuda.set_stream(stream)
+    sp = stream.cuda_stream
+
+    def step_params(i, flags):
+        return capi.RenderParams(WIDTH, HEIGHT, MAX_DEPTH, i * S * N + rank, S, N, flags, 0)
+
+    def dev_step(i, timing=True):
+        p = step_params(i, capi.RENDER_CLEAR | (capi.RENDER_STAGE_TIMING if timing else 0))
+        g.render_dev(p, d_sum.data_ptr(), 0, 0, sp)
+        if N > 1:
+            dist.reduce(d_sum, dst=0)
+        if rank == 0:
+            d_total.add_(d_sum)
+        return g.stats()
+
+    def barrier():
+        if N > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for i in range(args.warmup):
+        dev_step(i)
+    barrier()
+    clocks = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    rays_c = rays_a = launches = 0
+    ext_ms = con_ms = 0.0
+    ext_l = con_l = 0
+    per_step_rays_c = []
+    e0.record(stream)
+    for i in range(args.steps):
+        st = dev_step(args.warmup + i)
+        rays_c += st["rays_closest"]; rays_a += st["rays_any"]; launches += st["kernel_launches"] + (1 if rank == 0 else 0)
+        ext_ms += st["extend_ms"]; con_ms += st["connect_ms"]; ext_l += st["extend_launches"]; con_l += st["connect_launches"]
+        per_step_rays_c.append(st["rays_closest"])
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop() if clocks else None
+    t = torch.tensor([ms, float(rays_c), float(rays_a), float(launches)], dtype=torch.float64, device=dev)
+    if N > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms = float(tmax[0]); rays_c_all, rays_a_all, launches_all = float(tsum[1]), float(tsum[2]), float(tsum[3])
+    else:
+        rays_c_all, rays_a_all, launches_all = float(rays_c), float(rays_a), float(launches)
+    samples = float(n_px) * S * args.steps * N
+    value = samples / (ms * 1e-3) / 1e6
+    mrays = (rays_c_all + rays_a_all) / (ms * 1e-3) / 1e6
+
+    # ---- e2e: the same steps through the C ABI with HOST buffers (pinned), copies inside the call
+    h_sum = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32).pin_memory()
+    h_ptr = h_sum.data_ptr()
+
+    def e2e_step(i):
+        # accumulate into the caller's host buffer: upload of the running sums + download of the new ones
+        p = step_params(i, capi.RENDER_HOST_BUFFERS | (capi.RENDER_CLEAR if N > 1 else 0))
+        g.render_dev(p, h_ptr, 0, 0, sp)
+        if N > 1:   # per-rank host result -> device -> NCCL reduce -> host on rank 0
+            d_sum.copy_(h_sum, non_blocking=True)
+            dist.reduce(d_sum, dst=0)
+            if rank == 0:
+                h_sum.copy_(d_sum, non_blocking=True)
+        torch.cuda.synchronize(dev)
+
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    e2e_step(0)
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.perf_counter()
+    f0.record(stream)
+    for i in range(e2e_steps):
+        e2e_step(args.warmup + i)
+    f1.record(stream)
+    barrier()
+    e2e_ms = max(f0.elapsed_time(f1), (time.perf_counter() - w0) * 1e3 if N == 1 else 0.0)
+    if N > 1:
+        tt = torch.tensor([e2e_ms], dtype=torch.float64, device=dev); dist.all_reduce(tt, op=dist.ReduceOp.MAX); e2e_ms = float(tt[0])
+    e2e_value = float(n_px) * S * e2e_steps * N / (e2e_ms * 1e-3) / 1e6
+    h2d = n_px * 16 + C.sizeof(capi.RenderParams)
+    d2h = n_px * 16
+
+    # ---- roofline of the dominant kernel (k_extend): algorithmic bytes from a counted pass (untimed)
+    roof = None
+    extra = {}
+    if rank == 0:
+        p = step_params(args.warmup, capi.RENDER_CLEAR | capi.RENDER_COUNTED)
+        g.render_dev(p, d_sum.data_ptr(), 0, 0, sp)
+        sc = g.stats()
+        rc, ra = max(1, sc["rays_closest"]), max(1, sc["rays_any"])
+        b_closest = 48.0 + (80.0 * sc["node_visits"] + 48.0 * sc["prim_tests_tri"] + 32.0 * sc["prim_tests_sphere"]) / rc
+        b_any = 33.0 + (80.0 * sc["node_visits_any"] + 48.0 * sc["prim_tests_tri_any"] + 32.0 * sc["prim_tests_sphere_any"]) / ra
+        peak, peak_src = peaks()
+        ach = rays_c * b_closest / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+        ach_any = rays_a * b_any / (con_ms * 1e-3) / 1e9 if con_ms > 0 else 0.0
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("k_extend_dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        roof = {"bound": "hbm", "kernel": "k_extend (closest-hit traversal of the 8-wide BVH)", "achieved": ach, "peak": peak,
+                "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
+                "bytes_per_ray": b_closest, "bytes_per_launch": rays_c * b_closest / max(1, ext_l),
+                "avg_launch_ms": ext_ms / max(1, ext_l), "launches": ext_l,
+                "nodes_per_ray": sc["node_visits"] / rc, "tris_per_ray": sc["prim_tests_tri"] / rc,
+                "spheres_per_ray": sc["prim_tests_sphere"] / rc,
+                "share_of_step": ext_ms / ms if N == 1 else None,
+                "bytes_from": "counted pass over the first timed step's frames (PB_RENDER_COUNTED), scaled by each step's ray count"}
+        extra["roofline_connect"] = {"bound": "hbm", "kernel": "k_connect (any-hit traversal)", "achieved": ach_any, "peak": peak,
+                                     "unit": "GB/s", "frac": ach_any / peak, "bytes_per_ray": b_any,
+                                     "avg_launch_ms": con_ms / max(1, con_l), "launches": con_l,
+                                     "share_of_step": con_ms / ms if N == 1 else None}
+        extra["mrays_per_s_closest_kernel"] = rays_c / (ext_ms * 1e-3) / 1e6 if ext_ms > 0 else None
+        extra["mrays_per_s_any_kernel"] = rays_a / (con_ms * 1e-3) / 1e6 if con_ms > 0 else None
+
+    # ---- CPU baseline (rank 0, N = 1 only): the oracle on the host cores, bounded sample
+    cpu = None
+    if rank == 0 and N == 1 and not args.no_cpu:
+        try:
+            cpu, _, _ = cpu_leg(args.mesh, mesh, 10.0, 2, 1, False)
+        except Exception as e:  # the baseline is a report, never a reason to lose the GPU line
+            cpu = {"value": None, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
+
+    if rank == 0:
+        line = {"metric": "Msamples/s at 1080p pt+MIS", "value": value, "unit": "Msamples/s", "n_gpus": N, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "mesh": args.mesh, "n_tris": info["n_tris"], "n_spheres": info["n_spheres"],
+                           "spp_per_step": S, "frames_per_gpu_per_step": S, "sharding": f"sample-interleaved x{N} + NCCL reduce" if N > 1 else "none",
+                           "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"},
+                "mrays_per_s": mrays, "rays_per_sample": (rays_c_all + rays_a_all) / samples,
+                "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
+                "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
+                "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}
+        line.update(extra)
+        print(json.dumps(line), flush=True)
+    if N > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="product", choices=["product", "reference"])
+    ap.add_argument("--spp-per-step", type=int, default=32)
+    ap.add_argument("--e2e-steps", type=int, default=4)
+    ap.add_argument("--mesh", default="10M", choices=["1M", "10M", "100M"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        return reference_main(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus != world and world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under torch.distributed.run, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return product_main(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -111,7 +111,11 @@ typedef struct pb_render_params {
 } pb_render_params;
 enum {
     PB_RENDER_HOST_BUFFERS = 1u, /* output pointers are host memory (copy included in the call)  */
-    PB_RENDER_CLEAR = 2u         /* zero the sum buffer first (sample_cnt = 0, pt_pass.cpp:43)   */
+    PB_RENDER_CLEAR = 2u,        /* zero the sum buffer first (sample_cnt = 0, pt_pass.cpp:43)   */
+    PB_RENDER_COUNTED = 4u,      /* instrumented traversal: fills the visit counters of pb_stats
+                                    (same image; never the timed build)                          */
+    PB_RENDER_STAGE_TIMING = 8u  /* CUDA events around every extend / connect launch: fills
+                                    extend_ms / connect_ms / *_launches of pb_stats               */
 };
 
 typedef struct pb_stats {
@@ -122,6 +126,12 @@ typedef struct pb_stats {
     uint32_t bvh_depth, n_objects;
     float    build_ms, last_render_ms, last_trace_ms;
     uint32_t kernel_launches;               /* product kernels launched by the last call         */
+    /* PB_RENDER_COUNTED: visits of the shadow (any-hit) rays; node_visits / prim_tests_* above
+     * then hold the closest-hit rays' visits only                                                */
+    uint64_t node_visits_any, prim_tests_tri_any, prim_tests_sphere_any;
+    /* PB_RENDER_STAGE_TIMING: summed device time of the traversal launches of the last render    */
+    float    extend_ms, connect_ms;
+    uint32_t extend_launches, connect_launches;
 } pb_stats;
 
 typedef struct pb_ctx pb_ctx;

@@ -20,7 +20,7 @@ TEX_RGB, TEX_BITMAP, TEX_CHECKERBOARD = 0, 1, 2
 MAT_DIFFUSE, MAT_DIELECTRIC, MAT_ROUGH_DIELECTRIC, MAT_CONDUCTOR, MAT_ROUGH_CONDUCTOR, MAT_PLASTIC, MAT_ROUGH_PLASTIC = range(1, 8)
 SHAPE_FLIP_NORMALS, SHAPE_FLIP_TEX_COORDS = 1, 2
 ENV_NONE, ENV_CONSTANT, ENV_MAP = 0, 1, 2
-RENDER_HOST_BUFFERS, RENDER_CLEAR = 1, 2
+RENDER_HOST_BUFFERS, RENDER_CLEAR, RENDER_COUNTED, RENDER_STAGE_TIMING = 1, 2, 4, 8
 MISS = 0xFFFFFFFF
 
 
@@ -55,7 +55,10 @@ class Stats(C.Structure):
                 ("n_prims", C.c_uint64), ("n_nodes", C.c_uint64), ("n_emitters", C.c_uint64),
                 ("bvh_depth", C.c_uint32), ("n_objects", C.c_uint32),
                 ("build_ms", C.c_float), ("last_render_ms", C.c_float), ("last_trace_ms", C.c_float),
-                ("kernel_launches", C.c_uint32)]
+                ("kernel_launches", C.c_uint32),
+                ("node_visits_any", C.c_uint64), ("prim_tests_tri_any", C.c_uint64), ("prim_tests_sphere_any", C.c_uint64),
+                ("extend_ms", C.c_float), ("connect_ms", C.c_float),
+                ("extend_launches", C.c_uint32), ("connect_launches", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

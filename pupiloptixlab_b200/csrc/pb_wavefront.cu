@@ -10,6 +10,7 @@
 // Path state is SoA in HBM (float4 per field), queues are compacted with warp ballots + one atomic
 // per warp, every kernel is persistent over a device-side counter so a wave needs no host sync.
 #include <algorithm>
+#include <vector>
 
 #include "pb_bsdf.cuh"
 #include "pb_emitter.cuh"
@@ -36,7 +37,7 @@ struct WfState {
     float4* sh_ray;     // 2 per shadow entry
     float4* sh_con;     // contribution.xyz, slot bits
     uint32_t* cnt;      // C_* counters
-    unsigned long long* totals;  // [0] closest rays, [1] any rays
+    unsigned long long* totals;  // [0] closest rays, [1] any rays, [2..4] closest node/tri/sphere visits, [5..7] any
     uint32_t cap;
 };
 
@@ -107,6 +108,7 @@ __global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_
 }
 
 // ---- extend: closest hit for every queued path, then bin by material --------------------------------
+template<bool COUNT>
 __global__ void __launch_bounds__(kWfThreads) k_extend(WfState s, WfScene sc, int cur) {
     __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
     LaneStack st;
@@ -114,6 +116,7 @@ __global__ void __launch_bounds__(kWfThreads) k_extend(WfState s, WfScene sc, in
     const uint32_t n = s.cnt[cur ? C_EXT_B : C_EXT_A];
     const uint32_t* q = s.q_ext[cur];
     const unsigned lane = threadIdx.x & 31u;
+    TraceCounters tc = {0ull, 0ull, 0ull};
     while (true) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(&s.cnt[C_CUR_EXT], 32u);
@@ -125,7 +128,7 @@ __global__ void __launch_bounds__(kWfThreads) k_extend(WfState s, WfScene sc, in
             slot = q[i];
             const float4 a = s.ray[2 * slot], b = s.ray[2 * slot + 1];
             Hit h;
-            traverse<false, false>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, nullptr);
+            traverse<false, COUNT>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, &tc);
             s.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
             s.hit_obj[slot] = h.obj;
             bin = h.prim == 0xFFFFFFFFu ? 0u : sc.mats[sc.geom.objs[h.obj].material].type;
@@ -136,15 +139,18 @@ __global__ void __launch_bounds__(kWfThreads) k_extend(WfState s, WfScene sc, in
             if (bin == b) s.q_mat[(size_t)b * s.cap + pos] = slot;
         }
     }
+    if (COUNT) { atomicAdd(&s.totals[2], tc.nodes); atomicAdd(&s.totals[3], tc.tris); atomicAdd(&s.totals[4], tc.spheres); }
 }
 
 // ---- connect: any hit for the shadow queue; unoccluded contributions go to the path radiance --------
+template<bool COUNT>
 __global__ void __launch_bounds__(kWfThreads) k_connect(WfState s, WfScene sc) {
     __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
     LaneStack st;
     st.init(s_stack + threadIdx.x, kWfThreads);
     const uint32_t n = s.cnt[C_SHADOW];
     const unsigned lane = threadIdx.x & 31u;
+    TraceCounters tc = {0ull, 0ull, 0ull};
     while (true) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(&s.cnt[C_CUR_CON], 32u);
@@ -154,7 +160,7 @@ __global__ void __launch_bounds__(kWfThreads) k_connect(WfState s, WfScene sc) {
         if (i < n) {
             const float4 a = s.sh_ray[2 * i], b = s.sh_ray[2 * i + 1];
             Hit h;
-            traverse<true, false>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, nullptr);
+            traverse<true, COUNT>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, &tc);
             if (h.prim == 0xFFFFFFFFu) {
                 const float4 c = s.sh_con[i];
                 const uint32_t slot = __float_as_uint(c.w);
@@ -164,6 +170,7 @@ __global__ void __launch_bounds__(kWfThreads) k_connect(WfState s, WfScene sc) {
             }
         }
     }
+    if (COUNT) { atomicAdd(&s.totals[5], tc.nodes); atomicAdd(&s.totals[6], tc.tris); atomicAdd(&s.totals[7], tc.spheres); }
 }
 
 
@@ -355,7 +362,7 @@ static int wavefront_reserve(pb_ctx* c, uint32_t cap) {
     auto take = [&](size_t bytes) { size_t o = off; off += al(bytes); return o; };
     const size_t o_ray = take(n * 32), o_hit = take(n * 16), o_obj = take(n * 4), o_thr = take(n * 16), o_rad = take(n * 16),
                  o_flags = take(n * 4), o_q0 = take(n * 4), o_q1 = take(n * 4), o_qm = take(n * 4 * 8), o_shr = take(n * 32),
-                 o_shc = take(n * 16), o_cnt = take(C_COUNT * 4), o_tot = take(16);
+                 o_shc = take(n * 16), o_cnt = take(C_COUNT * 4), o_tot = take(64);
     PB_CUDA_TRY(c, cudaMalloc(&c->wf->block, off));
     char* b = static_cast<char*>(c->wf->block);
     WfState& s = c->wf->st;
@@ -396,7 +403,14 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
 
     cudaEvent_t e0, e1;
     PB_CUDA_TRY(c, cudaEventCreate(&e0)); PB_CUDA_TRY(c, cudaEventCreate(&e1));
-    PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 16, s));
+    PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 64, s));
+    const bool counted = (p->flags & PB_RENDER_COUNTED) != 0u, timing = (p->flags & PB_RENDER_STAGE_TIMING) != 0u;
+    std::vector<cudaEvent_t> ev_ext, ev_con;   // begin/end pairs around every traversal launch
+    auto mark = [&](std::vector<cudaEvent_t>& v) {
+        if (!timing) return;
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, s); v.push_back(e); }
+    };
     cudaEventRecord(e0, s);
     const unsigned g_trace = (unsigned)c->sm_count * 8u, g_shade = (unsigned)c->sm_count * 8u;
     uint32_t launches = 0;
@@ -410,7 +424,10 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
         int cur = 0;
         for (uint32_t b = 0; b < std::max(1u, p->max_depth); ++b) {
             k_prepare<<<1, 1, 0, s>>>(st, cur, n_paths, b == 0 ? 1 : 0);
-            k_extend<<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
+            mark(ev_ext);
+            if (counted) k_extend<true><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
+            else k_extend<false><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
+            mark(ev_ext);
             k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, d_albedo, d_normal);
             launch_shade<1>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
             launch_shade<2>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
@@ -420,7 +437,10 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
             launch_shade<6>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
             launch_shade<7>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
             k_after_shade<<<1, 1, 0, s>>>(st);
-            k_connect<<<g_trace, kWfThreads, 0, s>>>(st, sc);
+            mark(ev_con);
+            if (counted) k_connect<true><<<g_trace, kWfThreads, 0, s>>>(st, sc);
+            else k_connect<false><<<g_trace, kWfThreads, 0, s>>>(st, sc);
+            mark(ev_con);
             launches += 12;
             cur ^= 1;
         }
@@ -428,8 +448,8 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
         ++launches;
     }
     cudaEventRecord(e1, s);
-    unsigned long long tot[2];
-    PB_CUDA_TRY(c, cudaMemcpyAsync(tot, st.totals, 16, cudaMemcpyDeviceToHost, s));
+    unsigned long long tot[8];
+    PB_CUDA_TRY(c, cudaMemcpyAsync(tot, st.totals, 64, cudaMemcpyDeviceToHost, s));
     PB_CUDA_TRY(c, cudaStreamSynchronize(s));
     PB_CUDA_TRY(c, cudaGetLastError());
     float ms = 0.f;
@@ -439,6 +459,16 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     c->stats.rays_closest = tot[0]; c->stats.rays_any = tot[1];
     c->stats.samples = (uint64_t)n_px * p->sample_count;
     c->stats.kernel_launches = launches;
+    c->stats.node_visits = tot[2]; c->stats.prim_tests_tri = tot[3]; c->stats.prim_tests_sphere = tot[4];
+    c->stats.node_visits_any = tot[5]; c->stats.prim_tests_tri_any = tot[6]; c->stats.prim_tests_sphere_any = tot[7];
+    auto sum_pairs = [](std::vector<cudaEvent_t>& v) {
+        float total = 0.f;
+        for (size_t i = 0; i + 1 < v.size(); i += 2) { float t = 0.f; cudaEventElapsedTime(&t, v[i], v[i + 1]); total += t; }
+        for (cudaEvent_t e : v) cudaEventDestroy(e);
+        return total;
+    };
+    c->stats.extend_launches = (uint32_t)(ev_ext.size() / 2); c->stats.connect_launches = (uint32_t)(ev_con.size() / 2);
+    c->stats.extend_ms = sum_pairs(ev_ext); c->stats.connect_ms = sum_pairs(ev_con);
     return PB_OK;
 }
 
