@@ -1,6 +1,7 @@
 // pb_capi.cu — the C ABI of include/pupil_b200.h: context lifetime and scene ingestion.
 // (commit / trace / render entry points are in pb_commit.cu.)  There is no CPU fallback: without a
 // CUDA device pb_create fails with PB_ERR_NO_DEVICE.
+#include <cstdlib>
 #include <cstring>
 
 #include "pb_internal.h"
@@ -30,6 +31,7 @@ PB_API int pb_create(pb_ctx** out, int device) {
     cudaDeviceProp prop;
     PB_CUDA_TRY(c, cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
+    if (const char* e = getenv("PB_REFILL")) { int v = atoi(e); if (v >= 1 && v <= 32) c->refill = (uint32_t)v; }
     return PB_OK;
 }
 

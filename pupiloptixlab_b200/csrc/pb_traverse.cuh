@@ -27,6 +27,7 @@ struct TraceScene {
     const ObjRec* objs;
     float delta;
     uint32_t n_nodes;
+    uint32_t refill;      // refill idle lanes when fewer than this many lanes of a warp hold a ray
 };
 
 struct Hit { float t, u, v; uint32_t prim; uint32_t obj; };
@@ -47,19 +48,20 @@ inline int pop_cnt(uint32_t x) { return __builtin_popcount(x); }
 #endif
 
 #ifndef PB_SMEM_STACK
-#define PB_SMEM_STACK 8
+#define PB_SMEM_STACK 12
 #endif
-#define PB_LOCAL_STACK 56
+#define PB_LOCAL_STACK 52
 
 struct U2 { uint32_t x, y; };
 
-// Per-lane traversal stack: shared-memory head + local-memory tail.
+// Per-lane traversal stack: shared-memory head + local-memory tail.  The tail array is owned by the
+// kernel (not a member) so that `sp` is scalar-replaced into a register.
 struct LaneStack {
     U2* smem;          // this lane's first entry; entries are `stride` apart
+    U2* local;         // PB_LOCAL_STACK entries
     uint32_t stride;
-    U2 local[PB_LOCAL_STACK];
     int sp;
-    PB_HD void init(U2* s, uint32_t st) { smem = s; stride = st; sp = 0; }
+    PB_HD void init(U2* s, uint32_t st, U2* tail) { smem = s; stride = st; local = tail; sp = 0; }
     PB_HD void push(U2 v) {
         if (sp < PB_SMEM_STACK) smem[sp * stride] = v;
         else local[sp - PB_SMEM_STACK] = v;
@@ -70,6 +72,14 @@ struct LaneStack {
         return sp < PB_SMEM_STACK ? smem[sp * stride] : local[sp - PB_SMEM_STACK];
     }
 };
+
+// byte j of w as an exact float: 0x4B0000bb is 2^23 + bb, minus 2^23 (one PRMT + one FADD instead
+// of the quarter-rate I2F.U8 the compiler emits for (float)(w >> 8j & 255))
+#if defined(__CUDA_ARCH__)
+template<int J> PB_D float byte_f(uint32_t w) { return __fsub_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u + J)), 8388608.0f); }
+#else
+template<int J> inline float byte_f(uint32_t w) { return (float)((w >> (8 * J)) & 0xffu); }
+#endif
 
 // hit mask of one node for this ray: bits 24..31 inner children (octant ordered), bits 0..23 prims
 PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3, const U4& n4, V3 o, const RayPre& pre,
@@ -83,45 +93,62 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
     const float by = f_mul(f_sub(u2f(n0.y), o.y), pre.id.y);
     const float bz = f_mul(f_sub(u2f(n0.z), o.z), pre.id.z);
     const bool nx = pre.id.x < 0.f, ny = pre.id.y < 0.f, nz = pre.id.z < 0.f;
+    const uint32_t octinv4 = octinv * 0x01010101u;
     uint32_t mask = 0;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
         const uint32_t meta4 = half ? n1.w : n1.z;
+        // per child byte (Ylitie et al. 2017, listing 1): inner children have bits 3 and 4 of meta set
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+        const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;   // inner: 24 + (slot ^ octinv)
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;                        // inner: 1, leaf: unary count, empty: 0
         const uint32_t lx = half ? n2.y : n2.x, ly = half ? n2.w : n2.z, lz = half ? n3.y : n3.x;
         const uint32_t hx = half ? n3.w : n3.z, hy = half ? n4.y : n4.x, hz = half ? n4.w : n4.z;
         const uint32_t qnx = nx ? hx : lx, qfx = nx ? lx : hx;
         const uint32_t qny = ny ? hy : ly, qfy = ny ? ly : hy;
         const uint32_t qnz = nz ? hz : lz, qfz = nz ? lz : hz;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const uint32_t meta = (meta4 >> (8 * j)) & 0xffu;
-            if (meta == 0u) continue;
-            const int sh = 8 * j;
-            float tnx = f_fma((float)((qnx >> sh) & 0xffu), ax, bx), tfx = f_fma((float)((qfx >> sh) & 0xffu), ax, bx);
-            float tny = f_fma((float)((qny >> sh) & 0xffu), ay, by), tfy = f_fma((float)((qfy >> sh) & 0xffu), ay, by);
-            float tnz = f_fma((float)((qnz >> sh) & 0xffu), az, bz), tfz = f_fma((float)((qfz >> sh) & 0xffu), az, bz);
-            float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-            float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-            if (tn <= tf) {
-                const uint32_t low5 = meta & 31u;
-                if (low5 >= 24u) mask |= 1u << (24u + ((low5 - 24u) ^ octinv));   // inner child
-                else mask |= (meta >> 5) << low5;                                  // leaf: unary count bits
-            }
+#define PB_CHILD(J)                                                                                              \
+        {                                                                                                        \
+            const float tnx = f_fma(byte_f<J>(qnx), ax, bx), tfx = f_fma(byte_f<J>(qfx), ax, bx);               \
+            const float tny = f_fma(byte_f<J>(qny), ay, by), tfy = f_fma(byte_f<J>(qfy), ay, by);               \
+            const float tnz = f_fma(byte_f<J>(qnz), az, bz), tfz = f_fma(byte_f<J>(qfz), az, bz);               \
+            const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                           \
+            const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                           \
+            const uint32_t bits = ((child_bits4 >> (8 * J)) & 0xffu) << ((bit_index4 >> (8 * J)) & 0xffu);      \
+            mask |= tn <= tf ? bits : 0u;                                                                        \
         }
+        PB_CHILD(0) PB_CHILD(1) PB_CHILD(2) PB_CHILD(3)
+#undef PB_CHILD
     }
     return mask;
 }
 
+// Resumable traversal of one ray: begin() once, then step() until it returns true.  One step = one
+// node visit (8 child boxes) plus the primitives of the leaf children it hit.  Kernels interleave
+// steps of 32 rays per warp and refill finished lanes between steps (pb_trace_loop.cuh).
 template<bool ANY, bool COUNT>
-PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hit& best, LaneStack& st, TraceCounters* cnt) {
-    best.t = tmax; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu; best.obj = 0xFFFFFFFFu;
-    if (sc.n_nodes == 0) return;
-    const RayPre pre = ray_pre(o, d);
-    const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
-    const uint32_t octinv = 7u - oct;
-    U2 G = {0u, 0x80000000u};
-    st.sp = 0;
-    while (true) {
+struct Traversal {
+    V3 o, d;
+    float tmin, tmax;   // tmax = the ray's own bound (ties on t need it; best.t only orders)
+    RayPre pre;
+    uint32_t octinv;
+    U2 G;
+    Hit best;
+
+    PB_HD void begin(const TraceScene& sc, V3 o_, V3 d_, float tmin_, float tmax_, LaneStack& st) {
+        o = o_; d = d_; tmin = tmin_; tmax = tmax_;
+        best.t = tmax_; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu; best.obj = 0xFFFFFFFFu;
+        pre = ray_pre(o, d);
+        const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
+        octinv = 7u - oct;
+        G = {0u, sc.n_nodes ? 0x80000000u : 0u};
+        st.sp = 0;
+    }
+    PB_HD bool finished_at_begin() const { return (G.y & 0xff000000u) == 0u; }
+
+    // returns true when the ray is finished (best holds the result)
+    PB_HD bool step(const TraceScene& sc, LaneStack& st, TraceCounters* cnt) {
         U2 P = {0u, 0u};
         if (G.y & 0xff000000u) {
             const int bit = hi_bit(G.y);
@@ -149,15 +176,25 @@ PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hi
             float t, u, v;
             if (prim_accept(r, sc.objs, o, d, pre, tmin, tmax, sc.delta, t, u, v)) {
                 const uint32_t id = f2u(r.a.w);
-                if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); return; }
+                if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); return true; }
                 if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); }
             }
         }
         if (!(G.y & 0xff000000u)) {
-            if (st.sp == 0) break;
+            if (st.sp == 0) return true;
             G = st.pop();
         }
+        return false;
     }
+};
+
+template<bool ANY, bool COUNT>
+PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hit& best, LaneStack& st, TraceCounters* cnt) {
+    Traversal<ANY, COUNT> tr;
+    tr.begin(sc, o, d, tmin, tmax, st);
+    if (!tr.finished_at_begin())
+        while (!tr.step(sc, st, cnt)) {}
+    best = tr.best;
 }
 
 }  // namespace pb

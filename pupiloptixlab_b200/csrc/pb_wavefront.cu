@@ -16,6 +16,7 @@
 #include "pb_emitter.cuh"
 #include "pb_geom.cuh"
 #include "pb_internal.h"
+#include "pb_trace_loop.cuh"
 
 namespace pb {
 
@@ -108,68 +109,80 @@ __global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_
 }
 
 // ---- extend: closest hit for every queued path, then bin by material --------------------------------
+struct ExtendIO {
+    WfState s;
+    const ObjRec* __restrict__ objs;
+    const MatRec* __restrict__ mats;
+    const uint32_t* __restrict__ q;
+    uint32_t slot, pend_slot, pend_bin;   // per lane: current path, finished path waiting for its queue slot
+    __device__ __forceinline__ bool load(uint32_t i, V3& o, V3& d, float& tmin, float& tmax) {
+        slot = q[i];
+        const float4 a = s.ray[2 * slot], b = s.ray[2 * slot + 1];
+        o = {a.x, a.y, a.z}; d = {b.x, b.y, b.z}; tmin = a.w; tmax = b.w;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t, const Hit& h) {
+        s.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+        s.hit_obj[slot] = h.obj;
+        pend_slot = slot;
+        pend_bin = h.prim == 0xFFFFFFFFu ? 0u : mats[objs[h.obj].material].type;
+    }
+    // warp-aggregated append of the finished paths to their material queues (all lanes call)
+    __device__ __forceinline__ void flush() {
+        if (!__any_sync(0xFFFFFFFFu, pend_bin < 8u)) return;
+        const unsigned lane = threadIdx.x & 31u;
+        const unsigned peers = __match_any_sync(0xFFFFFFFFu, pend_bin);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if (pend_bin < 8u && (int)lane == leader) base = atomicAdd(&s.cnt[C_MAT0 + pend_bin], (uint32_t)__popc(peers));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        if (pend_bin < 8u) s.q_mat[(size_t)pend_bin * s.cap + base + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = pend_slot;
+        pend_bin = 8u;
+    }
+};
+
 template<bool COUNT>
 __global__ void __launch_bounds__(kWfThreads) k_extend(WfState s, WfScene sc, int cur) {
     __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
+    U2 tail[PB_LOCAL_STACK];
     LaneStack st;
-    st.init(s_stack + threadIdx.x, kWfThreads);
+    st.init(s_stack + threadIdx.x, kWfThreads, tail);
     const uint32_t n = s.cnt[cur ? C_EXT_B : C_EXT_A];
-    const uint32_t* q = s.q_ext[cur];
-    const unsigned lane = threadIdx.x & 31u;
     TraceCounters tc = {0ull, 0ull, 0ull};
-    while (true) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(&s.cnt[C_CUR_EXT], 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const uint32_t i = base + lane;
-        uint32_t bin = 8u, slot = 0u;
-        if (i < n) {
-            slot = q[i];
-            const float4 a = s.ray[2 * slot], b = s.ray[2 * slot + 1];
-            Hit h;
-            traverse<false, COUNT>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, &tc);
-            s.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-            s.hit_obj[slot] = h.obj;
-            bin = h.prim == 0xFFFFFFFFu ? 0u : sc.mats[sc.geom.objs[h.obj].material].type;
-        }
-#pragma unroll
-        for (uint32_t b = 0; b < 8u; ++b) {   // warp-aggregated append, one queue at a time
-            const uint32_t pos = warp_append(&s.cnt[C_MAT0 + b], bin == b);
-            if (bin == b) s.q_mat[(size_t)b * s.cap + pos] = slot;
-        }
-    }
+    ExtendIO io{s, sc.geom.objs, sc.mats, cur ? s.q_ext[1] : s.q_ext[0], 0u, 0u, 8u};
+    trace_loop<false, COUNT>(sc.ts, io, st, &s.cnt[C_CUR_EXT], n, sc.ts.refill, tc);
     if (COUNT) { atomicAdd(&s.totals[2], tc.nodes); atomicAdd(&s.totals[3], tc.tris); atomicAdd(&s.totals[4], tc.spheres); }
 }
 
 // ---- connect: any hit for the shadow queue; unoccluded contributions go to the path radiance --------
+struct ConnectIO {
+    WfState s;
+    __device__ __forceinline__ bool load(uint32_t i, V3& o, V3& d, float& tmin, float& tmax) const {
+        const float4 a = s.sh_ray[2 * i], b = s.sh_ray[2 * i + 1];
+        o = {a.x, a.y, a.z}; d = {b.x, b.y, b.z}; tmin = a.w; tmax = b.w;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+        if (h.prim != 0xFFFFFFFFu) return;
+        const float4 c = s.sh_con[i];
+        const uint32_t slot = __float_as_uint(c.w);
+        float4 r = s.rad[slot];
+        r.x += c.x; r.y += c.y; r.z += c.z;   // one shadow ray per path per bounce: no race
+        s.rad[slot] = r;
+    }
+    __device__ __forceinline__ void flush() const {}
+};
+
 template<bool COUNT>
 __global__ void __launch_bounds__(kWfThreads) k_connect(WfState s, WfScene sc) {
     __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
+    U2 tail[PB_LOCAL_STACK];
     LaneStack st;
-    st.init(s_stack + threadIdx.x, kWfThreads);
+    st.init(s_stack + threadIdx.x, kWfThreads, tail);
     const uint32_t n = s.cnt[C_SHADOW];
-    const unsigned lane = threadIdx.x & 31u;
     TraceCounters tc = {0ull, 0ull, 0ull};
-    while (true) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(&s.cnt[C_CUR_CON], 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const uint32_t i = base + lane;
-        if (i < n) {
-            const float4 a = s.sh_ray[2 * i], b = s.sh_ray[2 * i + 1];
-            Hit h;
-            traverse<true, COUNT>(sc.ts, {a.x, a.y, a.z}, {b.x, b.y, b.z}, a.w, b.w, h, st, &tc);
-            if (h.prim == 0xFFFFFFFFu) {
-                const float4 c = s.sh_con[i];
-                const uint32_t slot = __float_as_uint(c.w);
-                float4 r = s.rad[slot];
-                r.x += c.x; r.y += c.y; r.z += c.z;   // one shadow ray per path per bounce: no race
-                s.rad[slot] = r;
-            }
-        }
-    }
+    ConnectIO io{s};
+    trace_loop<true, COUNT>(sc.ts, io, st, &s.cnt[C_CUR_CON], n, sc.ts.refill, tc);
     if (COUNT) { atomicAdd(&s.totals[5], tc.nodes); atomicAdd(&s.totals[6], tc.tris); atomicAdd(&s.totals[7], tc.spheres); }
 }
 
@@ -179,7 +192,7 @@ template<int MAT>
 __global__ void __launch_bounds__(kWfThreads) k_shade(WfState s, WfScene sc, int cur, uint32_t k_aov, float* albedo, float* normal) {
     const uint32_t n = s.cnt[C_MAT0 + MAT];
     const uint32_t* q = s.q_mat + (size_t)MAT * s.cap;
-    uint32_t* qnext = s.q_ext[cur ^ 1];
+    uint32_t* qnext = cur ? s.q_ext[0] : s.q_ext[1];
     uint32_t* next_count = &s.cnt[cur ? C_EXT_A : C_EXT_B];
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;

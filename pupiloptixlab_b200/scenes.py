@@ -235,7 +235,22 @@ def height_field(x, z, seed=1234):
 
 def displaced_mesh(n: int, seed: int = 1234):
     """(n+1)^2 grid over [-1,1]^2 in XZ, 2 n^2 triangles; vertex normals from central differences,
-    uv = grid coordinates.  n = 707 -> 1.0 M, 2236 -> 10.0 M, 7071 -> 100.0 M triangles."""
+    uv = grid coordinates.  n = 707 -> 1.0 M, 2236 -> 10.0 M, 7071 -> 100.0 M triangles.
+    PB_MESH_CACHE=<dir> keeps the arrays on disk between runs (bench convenience only)."""
+    import os
+    cache = os.environ.get("PB_MESH_CACHE")
+    path = os.path.join(cache, f"mesh_{n}_{seed}.npz") if cache else None
+    if path and os.path.exists(path):
+        z = np.load(path)
+        return z["pos"], z["nrm"], z["uv"], z["idx"]
+    mesh = _displaced_mesh(n, seed)
+    if path:
+        os.makedirs(cache, exist_ok=True)
+        np.savez(path, pos=mesh[0], nrm=mesh[1], uv=mesh[2], idx=mesh[3])
+    return mesh
+
+
+def _displaced_mesh(n: int, seed: int = 1234):
     g = np.linspace(-1.0, 1.0, n + 1)
     X, Z = np.meshgrid(g, g, indexing="xy")
     Y = height_field(X, Z, seed)

@@ -117,13 +117,14 @@ void hs_counters(HS* h, unsigned long long* out) { out[0] = h->cnt.nodes; out[1]
 
 static TraceScene scene_of(HS* h) {
     return TraceScene{reinterpret_cast<const U4*>(h->nodes.data()), reinterpret_cast<const V4*>(h->prims_out.data()),
-                      h->objs.data(), h->delta, (uint32_t)h->nodes.size()};
+                      h->objs.data(), h->delta, (uint32_t)h->nodes.size(), 32u};
 }
 void hs_trace_closest(HS* h, const float* rays, uint64_t n, float* hits /* t,u,v,prim bits */) {
     TraceScene sc = scene_of(h);
     U2 smem[PB_SMEM_STACK];
+    U2 tail[PB_LOCAL_STACK];
     LaneStack st;
-    st.init(smem, 1);
+    st.init(smem, 1, tail);
     h->cnt = TraceCounters{};
     for (uint64_t i = 0; i < n; ++i) {
         const float* r = rays + 8 * i;
@@ -135,8 +136,9 @@ void hs_trace_closest(HS* h, const float* rays, uint64_t n, float* hits /* t,u,v
 void hs_trace_any(HS* h, const float* rays, uint64_t n, uint8_t* occ) {
     TraceScene sc = scene_of(h);
     U2 smem[PB_SMEM_STACK];
+    U2 tail[PB_LOCAL_STACK];
     LaneStack st;
-    st.init(smem, 1);
+    st.init(smem, 1, tail);
     h->cnt = TraceCounters{};
     for (uint64_t i = 0; i < n; ++i) {
         const float* r = rays + 8 * i;
