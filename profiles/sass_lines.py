@@ -38,3 +38,13 @@ ti = sum(a[0] for a in agg.values()); ts = sum(a[2] for a in agg.values()); tt =
 print(f"total warp inst {ti}, thread inst {tt}, lanes/inst {tt / ti:.2f}, samples {ts}")
 for loc, a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
     print(f"{100 * a[0] / ti:5.1f}% inst  lanes={a[1] / max(1, a[0]):5.1f}  {100 * a[2] / max(1, ts):5.1f}% samples  {loc}")
+print("---- by thread instructions")
+for loc, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:top]:
+    print(f"{100 * a[1] / tt:5.1f}% thr-inst  {100 * a[0] / ti:5.1f}% warp-inst lanes={a[1] / max(1, a[0]):5.1f}  {loc}")
+files = collections.defaultdict(lambda: [0, 0, 0])
+for loc, a in agg.items():
+    f = files[loc[0] if loc else None]
+    for k in range(3): f[k] += a[k]
+print("---- by file")
+for f, a in sorted(files.items(), key=lambda kv: -kv[1][0]):
+    print(f"{100 * a[0] / ti:5.1f}% warp-inst {100 * a[1] / tt:5.1f}% thr-inst {100 * a[2] / max(1, ts):5.1f}% samples lanes={a[1] / max(1, a[0]):5.1f} {f}")

@@ -36,6 +36,7 @@ struct BuildArrays {
     uint32_t* first; uint32_t* last;      // sorted range of each internal node
     V3* ilo; V3* ihi;                     // internal boxes
     uint32_t* flag;                       // arrival counters
+    uint32_t bottom_max;                  // subtrees with at most this many primitives become ONE wide node (<= 24)
 };
 
 PB_HD unsigned long long expand21(uint32_t v) {  // spread 21 bits to every third bit

@@ -28,39 +28,69 @@ PB_HD float half_area(V3 lo, V3 hi) {
     V3 e = hi - lo;
     return e.x * e.y + e.y * e.z + e.z * e.x;
 }
-PB_HD bool ref_is_inner_wide(const BuildArrays& b, uint32_t ref) {  // becomes an inner child of the wide node
-    return !(ref & kLeafFlag) && ref_count(b, ref) > kLeafMax;
+
+// Plan entries ("slot refs"): an inner child is the index of a binary internal node (< 2^29, no
+// flag); a leaf slot is a RANGE of the sorted primitive order: kLeafFlag | count << 29 | first,
+// count = 1..3.
+PB_HD uint32_t range_ref(uint32_t first, uint32_t count) { return kLeafFlag | (count << 29) | first; }
+PB_HD uint32_t range_first(uint32_t ref) { return ref & 0x1fffffffu; }
+PB_HD uint32_t range_count(uint32_t ref) { return (ref >> 29) & 3u; }
+PB_HD void slot_box(const BuildArrays& b, uint32_t ref, V3& lo, V3& hi) {
+    if (!(ref & kLeafFlag)) { lo = b.ilo[ref]; hi = b.ihi[ref]; return; }
+    const uint32_t first = range_first(ref), cnt = range_count(ref);
+    uint32_t p = b.order[first];
+    lo = b.blo[p]; hi = b.bhi[p];
+    for (uint32_t j = 1; j < cnt; ++j) {
+        p = b.order[first + j];
+        lo = {fminf(lo.x, b.blo[p].x), fminf(lo.y, b.blo[p].y), fminf(lo.z, b.blo[p].z)};
+        hi = {fmaxf(hi.x, b.bhi[p].x), fmaxf(hi.y, b.bhi[p].y), fmaxf(hi.z, b.bhi[p].z)};
+    }
 }
 
 PB_HD void collapse_plan(const BuildArrays& b, const CollapseArrays& c, uint32_t w) {
     uint32_t ch[8];
     int n = 0;
     const uint32_t root = c.work[w].bin_ref;
-    if (root & kLeafFlag) { ch[n++] = root; }            // single-primitive scene
-    else { ch[n++] = b.left[root]; ch[n++] = b.right[root]; }
-    // pass 0 opens nodes that would become inner children, pass 1 opens small subtrees so that
-    // leaf slots hold fewer primitives with tighter boxes
-    for (int pass = 0; pass < 2; ++pass) {
-        while (n < 8) {
-            int best = -1;
-            float best_area = -1.f;
-            for (int k = 0; k < n; ++k) {
-                if (ch[k] & kLeafFlag) continue;
-                const bool big = ref_count(b, ch[k]) > kLeafMax;
-                if ((pass == 0) != big) continue;
-                float a = half_area(b.ilo[ch[k]], b.ihi[ch[k]]);
-                if (a > best_area) { best_area = a; best = k; }
+    uint32_t ni = 0, np = 0;
+    if (root & kLeafFlag) {                                    // single-primitive scene
+        ch[n++] = range_ref(root & ~kLeafFlag, 1u);
+    } else if (ref_count(b, root) <= b.bottom_max) {
+        // bottom node: the whole subtree (a contiguous run of the Morton order) in one wide node,
+        // cut into <= 8 runs of ceil(count / 8) <= 3 primitives; no sparse inner nodes below it
+        const uint32_t cnt = ref_count(b, root), first = b.first[root], g = (cnt + 7u) / 8u;
+        for (uint32_t s0 = 0; s0 < cnt; s0 += g) ch[n++] = range_ref(first + s0, cnt - s0 < g ? cnt - s0 : g);
+    } else {
+        uint32_t bin[8];
+        bin[n++] = b.left[root]; bin[n++] = b.right[root];
+        // pass 0 opens nodes that would become inner children, pass 1 opens small subtrees so that
+        // leaf slots hold fewer primitives with tighter boxes
+        for (int pass = 0; pass < 2; ++pass) {
+            while (n < 8) {
+                int best = -1;
+                float best_area = -1.f;
+                for (int k = 0; k < n; ++k) {
+                    if (bin[k] & kLeafFlag) continue;
+                    const bool big = ref_count(b, bin[k]) > kLeafMax;
+                    if ((pass == 0) != big) continue;
+                    float a = half_area(b.ilo[bin[k]], b.ihi[bin[k]]);
+                    if (a > best_area) { best_area = a; best = k; }
+                }
+                if (best < 0) break;
+                const uint32_t r = bin[best];
+                bin[best] = b.left[r];
+                bin[n++] = b.right[r];
             }
-            if (best < 0) break;
-            const uint32_t r = ch[best];
-            ch[best] = b.left[r];
-            ch[n++] = b.right[r];
+        }
+        for (int k = 0; k < n; ++k) {
+            const uint32_t r = bin[k];
+            if (r & kLeafFlag) ch[k] = range_ref(r & ~kLeafFlag, 1u);
+            else if (ref_count(b, r) <= kLeafMax) ch[k] = range_ref(b.first[r], ref_count(b, r));
+            else ch[k] = r;
         }
     }
-    uint32_t ni = 0, np = 0;
     for (int k = 0; k < 8; ++k) {
         c.plan[8 * w + k] = k < n ? ch[k] : kNoRef;
-        if (k < n) { if (ref_is_inner_wide(b, ch[k])) ++ni; else np += ref_count(b, ch[k]); }
+        if (k < n) { if (ch[k] & kLeafFlag) np += range_count(ch[k]); else ++ni; }
     }
     c.cnt_inner[w] = ni;
     c.cnt_prims[w] = np;
@@ -85,7 +115,7 @@ PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t
         uint32_t r = c.plan[8 * w + k];
         if (r == kNoRef) break;
         ch[n] = r;
-        ref_box(b, r, clo[n], chi[n]);
+        slot_box(b, r, clo[n], chi[n]);
         ++n;
     }
     V3 lo = clo[0], hi = chi[0];
@@ -141,14 +171,13 @@ PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t
         auto qhi = [](float v, double p, double sc) { double q = ceil(((double)v - p) / sc); return (uint8_t)(q < 0.0 ? 0.0 : (q > 255.0 ? 255.0 : q)); };
         nd.qlox[s] = qlo(clo[k].x, lo.x, sx); nd.qloy[s] = qlo(clo[k].y, lo.y, sy); nd.qloz[s] = qlo(clo[k].z, lo.z, sz);
         nd.qhix[s] = qhi(chi[k].x, lo.x, sx); nd.qhiy[s] = qhi(chi[k].y, lo.y, sy); nd.qhiz[s] = qhi(chi[k].z, lo.z, sz);
-        if (ref_is_inner_wide(b, ch[k])) {
+        if (!(ch[k] & kLeafFlag)) {
             imask |= 1u << s;
             nd.meta[s] = (uint8_t)(0x20u | (24u + (uint32_t)s));
             c.next_work[off_inner + inner_rank] = {ch[k], c.next_wide_base + off_inner + inner_rank};
             ++inner_rank;
         } else {
-            const uint32_t cnt = ref_count(b, ch[k]);
-            const uint32_t first = (ch[k] & kLeafFlag) ? (ch[k] & ~kLeafFlag) : b.first[ch[k]];
+            const uint32_t cnt = range_count(ch[k]), first = range_first(ch[k]);
             nd.meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | prim_off);
             for (uint32_t j = 0; j < cnt; ++j)
                 c.prims_out[c.prim_cursor + off_prims + prim_off + j] = b.prims_in[b.order[first + j]];

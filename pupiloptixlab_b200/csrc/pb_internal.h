@@ -64,11 +64,13 @@ struct pb_ctx {
     unsigned long long* d_counters = nullptr;   // [0] ray fetch cursor, [1..3] visit counters
     pb::Wavefront* wf = nullptr;
     int sm_count = 148;
+    uint32_t bottom_max = 8;             // BVH collapse: subtrees up to this size become one wide node (PB_BOTTOM_MAX)
+    uint32_t prim_batch = 8;             // lanes holding primitives before a warp runs its primitive tests (PB_PRIM_BATCH)
     uint32_t refill = 20;                // dynamic-fetch threshold (PB_REFILL overrides, tuning only)
     pb_stats stats{};
 
     pb::TraceScene trace_scene() const {
-        return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill};
+        return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill, prim_batch};
     }
 };
 

@@ -96,19 +96,24 @@ PB_HD void pad_box(V3& lo, V3& hi, float d) {
 }
 
 // Full acceptance test of one primitive record.  objs = object table (for the sphere's Minv).
+// The slab interval [N, F] of B_in is evaluated FIRST: acceptance needs N <= t <= F, so an empty
+// interval, F <= tmin, N >= tmax or N > t_best (t_best = closest accepted t so far; ties on t_best
+// must still be tested) rejects without touching the primitive test — same accepted set, and the
+// sphere's dependent Minv fetch is skipped for most leaf-slot neighbours.
 PB_HD bool prim_accept(const PrimRec& r, const ObjRec* objs, V3 o, V3 d, const RayPre& pre, float tmin, float tmax,
-                       float delta, float& t, float& u, float& v) {
+                       float t_best, float delta, float& t, float& u, float& v) {
+    V3 lo, hi;
+    prim_bbox(r, lo, hi);
+    pad_box(lo, hi, delta);
+    float N, F;
+    slab(pre, lo, hi, N, F);
+    if (!(N <= F) || !(F > tmin) || !(N < tmax) || N > t_best) return false;
     if (f2u(r.c.w) == PRIM_TRI) {
         if (!tri_test(o, d, tmin, tmax, {r.a.x, r.a.y, r.a.z}, {r.b.x, r.b.y, r.b.z}, {r.c.x, r.c.y, r.c.z}, t, u, v)) return false;
     } else {
         u = 0.f; v = 0.f;
         if (!sphere_test(o, d, tmin, tmax, objs[f2u(r.b.w)].Minv, t)) return false;
     }
-    V3 lo, hi;
-    prim_bbox(r, lo, hi);
-    pad_box(lo, hi, delta);
-    float N, F;
-    slab(pre, lo, hi, N, F);
     return N <= t && t <= F;
 }
 

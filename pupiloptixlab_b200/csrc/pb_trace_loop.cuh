@@ -51,7 +51,7 @@ __device__ __forceinline__ void trace_loop(const TraceScene& sc, IO& io, LaneSta
             continue;
         }
         while (true) {
-            if (have && tr.step(sc, st, &tc)) { io.store(idx, tr.best); have = false; }
+            if (tr.step(sc, st, &tc, have)) { io.store(idx, tr.best); have = false; }   // all lanes call step()
             const unsigned m = __ballot_sync(0xFFFFFFFFu, have);
             if (m == 0u || (!exhausted && (uint32_t)__popc(m) < refill)) break;
         }

@@ -28,6 +28,7 @@ struct TraceScene {
     float delta;
     uint32_t n_nodes;
     uint32_t refill;      // refill idle lanes when fewer than this many lanes of a warp hold a ray
+    uint32_t prim_batch;  // run the primitive tests once this many lanes of a warp hold primitives
 };
 
 struct Hit { float t, u, v; uint32_t prim; uint32_t obj; };
@@ -124,16 +125,21 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
     return mask;
 }
 
-// Resumable traversal of one ray: begin() once, then step() until it returns true.  One step = one
-// node visit (8 child boxes) plus the primitives of the leaf children it hit.  Kernels interleave
-// steps of 32 rays per warp and refill finished lanes between steps (pb_trace_loop.cuh).
+// Resumable traversal of one ray: begin() once, then step() until it returns true.  One step = at
+// most one node visit (8 child boxes) and, when the warp decides so, the primitives found so far.
+// Kernels interleave steps of 32 rays per warp and refill finished lanes between steps
+// (pb_trace_loop.cuh).  On the device step() is called by ALL 32 lanes (alive or not): a lane that
+// has found primitives waits (takes no further nodes, so the visiting order is unchanged) until at
+// least `prim_batch` lanes of the warp hold primitives or no lane can advance through nodes any
+// more; the primitive tests then run with many lanes instead of the 2.6 / 32 measured before
+// (profiles/r01_extend.md).
 template<bool ANY, bool COUNT>
 struct Traversal {
     V3 o, d;
     float tmin, tmax;   // tmax = the ray's own bound (ties on t need it; best.t only orders)
     RayPre pre;
     uint32_t octinv;
-    U2 G;
+    U2 G, P;            // pending node group / primitive group
     Hit best;
 
     PB_HD void begin(const TraceScene& sc, V3 o_, V3 d_, float tmin_, float tmax_, LaneStack& st) {
@@ -143,14 +149,14 @@ struct Traversal {
         const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
         octinv = 7u - oct;
         G = {0u, sc.n_nodes ? 0x80000000u : 0u};
+        P = {0u, 0u};
         st.sp = 0;
     }
     PB_HD bool finished_at_begin() const { return (G.y & 0xff000000u) == 0u; }
 
-    // returns true when the ray is finished (best holds the result)
-    PB_HD bool step(const TraceScene& sc, LaneStack& st, TraceCounters* cnt) {
-        U2 P = {0u, 0u};
-        if (G.y & 0xff000000u) {
+    // returns true when the ray is finished (best holds the result); `alive` = this lane holds a ray
+    PB_HD bool step(const TraceScene& sc, LaneStack& st, TraceCounters* cnt, bool alive) {
+        if (alive && P.y == 0u) {   // invariant: an alive lane without primitives has inner hits in G
             const int bit = hi_bit(G.y);
             const uint32_t imask = G.y & 0xffu;
             G.y &= ~(1u << bit);
@@ -166,21 +172,30 @@ struct Traversal {
             P.x = n1.y;
             P.y = hits & 0x00ffffffu;
         }
-        while (P.y) {
-            const int i = lo_bit(P.y);
-            P.y &= P.y - 1u;
-            const V4* pp = sc.prims + 3ull * (P.x + (uint32_t)i);
-            PrimRec r;
-            r.a = ld_v4(pp); r.b = ld_v4(pp + 1); r.c = ld_v4(pp + 2);
-            if (COUNT) { if (f2u(r.c.w) == PRIM_TRI) cnt->tris++; else cnt->spheres++; }
-            float t, u, v;
-            if (prim_accept(r, sc.objs, o, d, pre, tmin, tmax, sc.delta, t, u, v)) {
-                const uint32_t id = f2u(r.a.w);
-                if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); return true; }
-                if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); }
-            }
+        const bool has_p = alive && P.y != 0u;
+#if defined(__CUDA_ARCH__)
+        const unsigned pm = __ballot_sync(0xFFFFFFFFu, has_p);
+        const bool do_prims = (uint32_t)__popc(pm) >= sc.prim_batch || pm == __ballot_sync(0xFFFFFFFFu, alive);
+#else
+        const bool do_prims = true;
+#endif
+        if (has_p && do_prims) {
+            do {
+                const int i = lo_bit(P.y);
+                P.y &= P.y - 1u;
+                const V4* pp = sc.prims + 3ull * (P.x + (uint32_t)i);
+                PrimRec r;
+                r.a = ld_v4(pp); r.b = ld_v4(pp + 1); r.c = ld_v4(pp + 2);
+                if (COUNT) { if (f2u(r.c.w) == PRIM_TRI) cnt->tris++; else cnt->spheres++; }
+                float t, u, v;
+                if (prim_accept(r, sc.objs, o, d, pre, tmin, tmax, best.t, sc.delta, t, u, v)) {
+                    const uint32_t id = f2u(r.a.w);
+                    if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); P.y = 0u; return true; }
+                    if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); }
+                }
+            } while (P.y);
         }
-        if (!(G.y & 0xff000000u)) {
+        if (alive && P.y == 0u && !(G.y & 0xff000000u)) {
             if (st.sp == 0) return true;
             G = st.pop();
         }
@@ -193,7 +208,7 @@ PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hi
     Traversal<ANY, COUNT> tr;
     tr.begin(sc, o, d, tmin, tmax, st);
     if (!tr.finished_at_begin())
-        while (!tr.step(sc, st, cnt)) {}
+        while (!tr.step(sc, st, cnt, true)) {}
     best = tr.best;
 }
 

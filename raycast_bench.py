@@ -1,0 +1,122 @@
+#!/usr/bin/env python
+"""raycast_bench.py — BASELINE.json configs[2] ("C3"): ray-cast microbench against the procedural
+displaced mesh (+ spheres): coherent primary rays and incoherent cosine-weighted bounce rays through
+pb_trace_closest / pb_trace_any with DEVICE buffers; reports Mrays/s, algorithmic bytes per ray
+(counted pass) and the HBM-roofline fraction.  `--check N` compares N rays of each set with the test
+oracle (bit-exact ids and t).  Not the headline bench (that is bench.py); one JSON line per ray set."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def bounce_rays(rays, hits, seed=1):
+    """One cosine-sampled bounce ray from every primary hit (geometric normal from the hit triangle is not
+    needed for a ray SET: the hemisphere is oriented around +Y flipped against the incoming ray)."""
+    from pupiloptixlab_b200 import capi
+    hit = hits["prim"] != capi.MISS
+    r, h = rays[hit], hits[hit]
+    n = len(r)
+    rng = np.random.RandomState(seed)
+    u1, u2 = rng.rand(n).astype(np.float32), rng.rand(n).astype(np.float32)
+    st, phi = np.sqrt(u1), 2 * np.pi * u2
+    lx, lz, ly = st * np.cos(phi), st * np.sin(phi), np.sqrt(np.maximum(0, 1 - u1))
+    out = np.zeros(n, capi.RAY_DTYPE)
+    out["ox"] = r["ox"] + h["t"] * r["dx"]; out["oy"] = r["oy"] + h["t"] * r["dy"]; out["oz"] = r["oz"] + h["t"] * r["dz"]
+    out["dx"], out["dy"], out["dz"] = lx, ly, lz
+    out["tmin"], out["tmax"] = 1e-3, 1e16
+    return out
+
+
+def morton_order(rays, lo=-1.0, hi=1.0):
+    def q(v):
+        return np.clip(((v - lo) / (hi - lo) * 1024).astype(np.int64), 0, 1023)
+    def spread(x):
+        x = (x | (x << 16)) & 0x030000FF
+        x = (x | (x << 8)) & 0x0300F00F
+        x = (x | (x << 4)) & 0x030C30C3
+        x = (x | (x << 2)) & 0x09249249
+        return x
+    k = (spread(q(rays["ox"])) << 2) | (spread(q(rays["oy"])) << 1) | spread(q(rays["oz"]))
+    return np.argsort(k, kind="stable")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mesh", default="10M")
+    ap.add_argument("--rays", type=int, default=20_000_000)
+    ap.add_argument("--spheres", type=int, default=0)
+    ap.add_argument("--check", type=int, default=0)
+    ap.add_argument("--reps", type=int, default=5)
+    args = ap.parse_args()
+    import torch
+    from pupiloptixlab_b200 import capi, scenes
+    api = capi.load()
+    g = capi.Context(api, 0)
+    n = scenes.MESH_N[args.mesh]
+    mesh = scenes.displaced_mesh(n)
+    info = scenes.bench_scene(g, n, args.spheres, 1920, 1080, patchwork=False, mesh=mesh)
+    side = int(np.sqrt(args.rays))
+    fov_y = scenes.fov_x_to_y(45.0, side, side)
+    s2c = scenes.perspective_sample_to_camera(fov_y, 1.0)
+    c2w = scenes.sensor_to_world(scenes.lookat_to_world(**{k: scenes.BENCH_CAMERA[k] for k in ("origin", "target", "up")}))
+    prim = scenes.camera_rays(s2c, c2w, side, side, 0)
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    dev = torch.device("cuda", 0)
+    stream = torch.cuda.Stream(dev); torch.cuda.set_stream(stream)
+
+    def run(name, rays, any_hit=False):
+        d_r = torch.from_numpy(rays.view(np.float32).reshape(-1, 8)).to(dev)
+        d_h = torch.empty((len(rays), 4), dtype=torch.float32, device=dev) if not any_hit else torch.empty(len(rays), dtype=torch.uint8, device=dev)
+        fn = g.trace_any_dev if any_hit else g.trace_closest_dev
+        for _ in range(3):
+            fn(d_r.data_ptr(), len(rays), d_h.data_ptr(), stream.cuda_stream)
+        ms = []
+        for _ in range(args.reps):
+            fn(d_r.data_ptr(), len(rays), d_h.data_ptr(), stream.cuda_stream)
+            ms.append(g.stats()["last_trace_ms"])
+        t = float(np.median(ms))
+        cnt_fn = g.api._trace_any_counted if any_hit else g.api._trace_closest_counted
+        g._ck(cnt_fn(g.h, d_r.data_ptr(), len(rays), d_h.data_ptr(), 0, stream.cuda_stream), "counted")
+        st = g.stats()
+        b = (32 + (1 if any_hit else 16)) + (80.0 * st["node_visits"] + 48.0 * st["prim_tests_tri"] + 32.0 * st["prim_tests_sphere"]) / len(rays)
+        out = {"set": name, "kernel": "k_trace<any>" if any_hit else "k_trace<closest>", "n_rays": len(rays), "mesh": args.mesh, "n_tris": info["n_tris"],
+               "spheres": args.spheres, "ms": t, "mrays_per_s": len(rays) / t / 1e3, "bytes_per_ray": b,
+               "nodes_per_ray": st["node_visits"] / len(rays), "tris_per_ray": st["prim_tests_tri"] / len(rays),
+               "roofline": {"bound": "hbm", "achieved": len(rays) * b / (t * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                            "frac": len(rays) * b / (t * 1e-3) / 1e9 / peak}}
+        print(json.dumps(out), flush=True)
+        res = d_h.cpu().numpy()
+        return res.view(capi.HIT_DTYPE).reshape(-1) if not any_hit else res
+
+    hp = run("coherent primary", prim)
+    inc = bounce_rays(prim, hp)
+    rng = np.random.RandomState(5)
+    inc = inc[rng.permutation(len(inc))]            # queue order of a wavefront after compaction: unordered
+    hi = run("incoherent bounce (unordered)", inc)
+    run("incoherent bounce (unordered), any-hit", inc, any_hit=True)
+    inc_s = inc[morton_order(inc)]
+    run("incoherent bounce (origin-Morton sorted)", inc_s)
+    if args.check:
+        from oracle import pyoracle
+        o = pyoracle.OracleContext(pyoracle.load())
+        scenes.bench_scene(o, n, args.spheres, 1920, 1080, patchwork=False, mesh=mesh)
+        for name, rays, got in (("coherent", prim, hp), ("incoherent", inc, hi)):
+            sel = np.random.RandomState(9).randint(0, len(rays), args.check)
+            want = o.trace_closest(rays[sel])
+            bad = int((want["prim"] != got["prim"][sel]).sum())
+            hit = want["prim"] != capi.MISS
+            bad_t = int((want["t"][hit].view(np.uint32) != got["t"][sel][hit].view(np.uint32)).sum())
+            print(json.dumps({"check": name, "rays": args.check, "id_mismatches": bad, "t_mismatches": bad_t, "hit_fraction": float(hit.mean())}), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -28,6 +28,9 @@ struct HS {
 
 extern "C" {
 
+static uint32_t hs_bottom_max = 16;
+void hs_set_bottom_max(uint32_t v) { hs_bottom_max = v; }
+
 HS* hs_create(const float* pos, uint32_t n_vert, const uint32_t* idx, uint32_t n_tri, const float* mesh_M,
               const float* sphere_M, uint32_t n_sph) {
     HS* h = new HS();
@@ -70,7 +73,7 @@ HS* hs_create(const float* pos, uint32_t n_vert, const uint32_t* idx, uint32_t n
     std::vector<unsigned long long> keys(n);
     std::vector<uint32_t> order(n), left(n), right(n), pint(n), pleaf(n), first(n), last(n), flag(n, 0);
     BuildArrays b{h->prims_in.data(), n, h->delta, slo, shi, blo.data(), bhi.data(), keys.data(), order.data(),
-                  left.data(), right.data(), pint.data(), pleaf.data(), first.data(), last.data(), ilo.data(), ihi.data(), flag.data()};
+                  left.data(), right.data(), pint.data(), pleaf.data(), first.data(), last.data(), ilo.data(), ihi.data(), flag.data(), hs_bottom_max};
     for (uint32_t i = 0; i < n; ++i) build_prim(b, i);
     // sort pairs (stands in for cub::DeviceRadixSort)
     std::vector<uint32_t> perm(n);
@@ -117,7 +120,7 @@ void hs_counters(HS* h, unsigned long long* out) { out[0] = h->cnt.nodes; out[1]
 
 static TraceScene scene_of(HS* h) {
     return TraceScene{reinterpret_cast<const U4*>(h->nodes.data()), reinterpret_cast<const V4*>(h->prims_out.data()),
-                      h->objs.data(), h->delta, (uint32_t)h->nodes.size(), 32u};
+                      h->objs.data(), h->delta, (uint32_t)h->nodes.size(), 32u, 1u};
 }
 void hs_trace_closest(HS* h, const float* rays, uint64_t n, float* hits /* t,u,v,prim bits */) {
     TraceScene sc = scene_of(h);
