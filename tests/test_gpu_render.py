@@ -84,3 +84,23 @@ def test_render_errors(api):
     g = capi.Context(api)
     with pytest.raises(capi.ApiError):
         g.render(8, 8, 4, 0, 1)          # not committed
+
+
+def test_cornell_matches_reference_header_golden_images(api):
+    """The CUDA path against images rendered by the REFERENCE's own BSDF/emitter/RNG headers
+    (tests/golden/reference_headers.npz, made by tests/golden/make_golden.py in the dev container)."""
+    from tests.golden import make_golden as G
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_headers.npz"))
+    for variant, w, h, depth, spp in G.RENDERS:
+        g = capi.Context(api)
+        scenes.cornell_box(g, w, h, variant)
+        sg, ag, ng = g.render(w, h, depth, 0, spp)
+        key = f"render_{variant}_{w}x{h}_d{depth}_s{spp}"
+        so = gold[key + "_sum"]
+        assert np.array_equal(sg[..., 3], so[..., 3])
+        frac = rel_ok_fraction(sg[..., :3], so[..., :3])
+        assert frac >= 0.998, f"{key}: only {frac:.5f} of the pixels within {REL_TOL}"
+        assert rel_ok_fraction(ag, gold[key + "_albedo"]) >= 0.998
+        assert rel_ok_fraction(ng, gold[key + "_normal"]) >= 0.998
+        rays = gold[key + "_rays"]
+        assert abs(int(g.stats()["rays_closest"]) - int(rays[0])) <= max(4, 3e-3 * int(rays[0]))
