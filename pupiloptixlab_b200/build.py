@@ -50,5 +50,30 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
     return OUT
 
 
+HOST_DIR = os.path.join(HERE, "host")
+HOST_OUT = os.path.join(HOST_DIR, "libpupil_host.so")
+HOST_SOURCES = ["scene_xml.cpp", "b200_pt_pass.cpp", "host_capi.cpp"]
+
+
+def build_host(force: bool = False) -> str:
+    """g++ build of the C++ host layer (scene XML loader, headless System/Pass, B200PTPass) ->
+    host/libpupil_host.so, linked against csrc/libpupil_b200.so ($ORIGIN rpath) and cudart."""
+    build_native()
+    deps = [os.path.join(HOST_DIR, f) for f in os.listdir(HOST_DIR) if f.endswith((".cpp", ".h"))]
+    deps += [os.path.join(os.path.dirname(HERE), "include", h) for h in ("pupil_b200.h", "pupil_host.h")] + [OUT]
+    if not force and _newer(HOST_OUT, deps):
+        return HOST_OUT
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-function", "-shared",
+           "-I", os.path.join(cuda, "include"), *[os.path.join(HOST_DIR, f) for f in HOST_SOURCES], "-o", HOST_OUT,
+           "-L", CSRC, "-lpupil_b200", "-L", os.path.join(cuda, "lib64"), "-lcudart", "-Wl,-rpath,$ORIGIN/../csrc",
+           "-Wl,-rpath," + os.path.join(cuda, "lib64")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("host layer build failed:\n" + r.stdout + r.stderr)
+    return HOST_OUT
+
+
 if __name__ == "__main__":
     print(build_native(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))

@@ -1,0 +1,76 @@
+// b200_pt_pass.cpp — see b200_pt_pass.h.
+#include "b200_pt_pass.h"
+
+namespace Pupil::pt {
+
+B200PTPass::B200PTPass(System* system, int device, std::string_view name) noexcept : Pass(name), m_system(system) {
+    // cuda::Context::Init + optix::Context::Init + PTPass ctor (pt_pass.cpp:29-37): one call
+    if (pb_create(&m_ctx, device) != PB_OK) { m_error = std::string("pb_create: ") + (m_ctx ? pb_last_error(m_ctx) : "no CUDA device (there is no CPU fallback)"); return; }
+    cudaSetDevice(device);
+    if (cudaStreamCreateWithFlags(&m_stream, cudaStreamNonBlocking) != cudaSuccess) m_error = "cudaStreamCreate failed";
+    BindingEventCallback();
+}
+
+B200PTPass::~B200PTPass() noexcept {
+    if (m_stream) cudaStreamDestroy(m_stream);
+    if (m_ctx) pb_destroy(m_ctx);
+}
+
+void B200PTPass::fail(const char* what) noexcept {
+    if (m_error.empty()) m_error = std::string(what) + ": " + (m_ctx ? pb_last_error(m_ctx) : "");
+    m_system->last_error = m_error;
+}
+
+// pt_pass.cpp:211-223
+void B200PTPass::BindingEventCallback() noexcept {
+    m_system->Bind(EWorldEvent::CameraChange, [this](void*) { m_dirty = true; });
+    m_system->Bind(EWorldEvent::RenderInstanceUpdate, [this](void*) { m_dirty = true; });
+    m_system->Bind(ESystemEvent::SceneLoad, [this](void* p) { SetScene(static_cast<world::World*>(p)); });
+}
+
+// pt_pass.cpp:107-209: launch config, output buffers, acceleration structure, "SBT" (= object / material /
+// emitter tables inside pb_scene_commit)
+void B200PTPass::SetScene(world::World* world) noexcept {
+    if (!m_ctx || !world || !world->scene) return;
+    m_world = world;
+    const pupil::host::Scene& sc = *world->scene;
+    std::string err;
+    const ph_sink* sink = ph_default_sink();
+    if (pupil::host::upload_scene(sc, *sink, m_ctx, err) != PB_OK) { m_error = err + ": " + pb_last_error(m_ctx); m_system->last_error = m_error; return; }
+    m_w = static_cast<uint32_t>(sc.film_w); m_h = static_cast<uint32_t>(sc.film_h);
+    max_depth = sc.max_depth;
+    BufferManager& bm = m_system->buffers;
+    m_frame = bm.GetBuffer(BufferManager::DEFAULT_FINAL_RESULT_BUFFER_NAME);
+    m_accum = bm.AllocBuffer({"pt accum buffer", EBufferFlag::None, m_w, m_h, sizeof(float) * 4});   // sums.xyz + frame count.w
+    m_albedo = bm.AllocBuffer({"albedo", EBufferFlag::AllowDisplay, m_w, m_h, sizeof(float) * 3});
+    m_normal = bm.AllocBuffer({"normal", EBufferFlag::AllowDisplay, m_w, m_h, sizeof(float) * 3});
+    if (!m_frame || !m_accum || !m_albedo || !m_normal) { m_error = "output buffer allocation failed"; m_system->last_error = m_error; return; }
+    m_dirty = true;
+}
+
+// pt_pass.cpp:39-57
+void B200PTPass::OnRun() noexcept {
+    if (!m_ctx || !m_world || !m_error.empty()) return;
+    if (m_dirty) {
+        const pupil::host::Mat4 s2c = m_world->camera.GetSampleToCameraMatrix(), c2w = m_world->camera.GetToWorldMatrix();
+        if (pb_set_camera(m_ctx, s2c.e, c2w.e) != PB_OK) return fail("pb_set_camera");
+        m_sample_cnt = 0;
+        m_random_seed = 0;
+        m_dirty = false;
+    }
+    pb_render_params p{};
+    p.width = m_w; p.height = m_h;
+    p.max_depth = static_cast<uint32_t>(max_depth);
+    p.first_sample = m_random_seed;                      // frame f of pixel p is seeded Init(4, p, f), main.cu:53
+    p.sample_count = frames_per_run;
+    p.sample_stride = 1;
+    p.flags = (m_sample_cnt == 0 || !accumulated_flag) ? PB_RENDER_CLEAR : 0u;
+    if (pb_render(m_ctx, &p, static_cast<float*>(m_accum->cuda_ptr), static_cast<float*>(m_albedo->cuda_ptr),
+                  static_cast<float*>(m_normal->cuda_ptr), m_stream) != PB_OK) return fail("pb_render");
+    if (pb_resolve(m_ctx, static_cast<const float*>(m_accum->cuda_ptr), static_cast<float*>(m_frame->cuda_ptr), m_w * m_h, 0, m_stream) != PB_OK)
+        return fail("pb_resolve");
+    if (accumulated_flag) m_sample_cnt += frames_per_run;   // sample_cnt += accumulated_flag (pt_pass.cpp:55)
+    m_random_seed += frames_per_run;                         // ++random_seed (pt_pass.cpp:56)
+}
+
+}  // namespace Pupil::pt

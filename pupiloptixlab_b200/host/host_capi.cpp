@@ -1,0 +1,118 @@
+// host_capi.cpp — the C entry points of libpupil_host.so (include/pupil_host.h).
+#include <cstring>
+
+#include "b200_pt_pass.h"
+#include "scene_xml.h"
+
+using namespace pupil::host;
+
+struct ph_scene { Scene scene; };
+static thread_local std::string g_err;
+
+static int sink_begin(void* c) { return pb_scene_begin(static_cast<pb_ctx*>(c)); }
+static int sink_mat(void* c, const pb_material* m, uint32_t* id) { return pb_add_material(static_cast<pb_ctx*>(c), m, id); }
+static int sink_mesh(void* c, const float* p, const float* n, const float* uv, uint32_t nv, const uint32_t* idx, uint32_t nt,
+                     const float tw[12], uint32_t fl, uint32_t mat, const pb_texture* rad, uint32_t* out) {
+    return pb_add_trimesh(static_cast<pb_ctx*>(c), p, n, uv, nv, idx, nt, tw, fl, mat, rad, out);
+}
+static int sink_sphere(void* c, const float tw[12], uint32_t fl, uint32_t mat, const pb_texture* rad, uint32_t* out) {
+    return pb_add_sphere(static_cast<pb_ctx*>(c), tw, fl, mat, rad, out);
+}
+static int sink_env(void* c, const pb_env* e) { return pb_set_env(static_cast<pb_ctx*>(c), e); }
+static int sink_cam(void* c, const float a[16], const float b[16]) { return pb_set_camera(static_cast<pb_ctx*>(c), a, b); }
+static int sink_commit(void* c) { return pb_scene_commit(static_cast<pb_ctx*>(c)); }
+static const ph_sink g_default_sink = {sink_begin, sink_mat, sink_mesh, sink_sphere, sink_env, sink_cam, sink_commit};
+
+extern "C" {
+
+PH_API const ph_sink* ph_default_sink(void) { return &g_default_sink; }
+PH_API const char* ph_last_error(void) { return g_err.c_str(); }
+
+PH_API int ph_scene_load_xml(const char* path, ph_scene** out) {
+    if (!path || !out) return PB_ERR_INVALID;
+    auto s = std::make_unique<ph_scene>();
+    if (!load_scene_xml_file(path, s->scene, g_err)) { *out = nullptr; return PB_ERR_INVALID; }
+    *out = s.release();
+    return PB_OK;
+}
+PH_API int ph_scene_load_xml_string(const char* xml, const char* root_dir, ph_scene** out) {
+    if (!xml || !out) return PB_ERR_INVALID;
+    auto s = std::make_unique<ph_scene>();
+    if (!load_scene_xml_text(xml, root_dir ? root_dir : "", s->scene, g_err)) { *out = nullptr; return PB_ERR_INVALID; }
+    *out = s.release();
+    return PB_OK;
+}
+PH_API void ph_scene_free(ph_scene* s) { delete s; }
+
+PH_API int ph_scene_info_get(const ph_scene* s, ph_scene_info* o) {
+    if (!s || !o) return PB_ERR_INVALID;
+    const Scene& sc = s->scene;
+    *o = ph_scene_info{};
+    o->max_depth = sc.max_depth; o->film_w = sc.film_w; o->film_h = sc.film_h;
+    o->fov_y = sc.fov; o->near_clip = sc.near_clip; o->far_clip = sc.far_clip;
+    o->n_shapes = static_cast<uint32_t>(sc.shape_instances.size());
+    for (auto& i : sc.shape_instances) {
+        if (i.is_emitter) ++o->n_emissive_shapes;
+        if (i.type == ShapeType::Sphere) ++o->n_spheres; else o->n_triangles += static_cast<uint32_t>(i.mesh->indices.size() / 3);
+    }
+    o->has_env = sc.has_env ? sc.env.type : PB_ENV_NONE;
+    o->n_warnings = static_cast<uint32_t>(sc.warnings.size());
+    return PB_OK;
+}
+PH_API const char* ph_scene_warning(const ph_scene* s, uint32_t i) { return s && i < s->scene.warnings.size() ? s->scene.warnings[i].c_str() : ""; }
+
+PH_API int ph_scene_camera(const ph_scene* s, float s2c[16], float c2w[16]) {
+    if (!s) return PB_ERR_INVALID;
+    const Camera cam = s->scene.camera();
+    std::memcpy(s2c, cam.GetSampleToCameraMatrix().e, 64);
+    std::memcpy(c2w, cam.GetToWorldMatrix().e, 64);
+    return PB_OK;
+}
+PH_API int ph_scene_shape(const ph_scene* s, uint32_t i, uint32_t* type, float tw[12], pb_material* mat, uint32_t* flags,
+                          uint32_t* is_emitter, pb_texture* radiance) {
+    if (!s || i >= s->scene.shape_instances.size()) return PB_ERR_INVALID;
+    const ShapeInstance& ins = s->scene.shape_instances[i];
+    if (type) *type = static_cast<uint32_t>(ins.type);
+    if (tw) std::memcpy(tw, ins.transform.matrix.e, 48);
+    if (mat) *mat = ins.mat;
+    if (flags) *flags = (ins.flip_normals ? PB_SHAPE_FLIP_NORMALS : 0u) | (ins.flip_tex_coords ? PB_SHAPE_FLIP_TEX_COORDS : 0u);
+    if (is_emitter) *is_emitter = ins.is_emitter ? 1u : 0u;
+    if (radiance) *radiance = ins.radiance;
+    return PB_OK;
+}
+PH_API int ph_scene_upload(const ph_scene* s, const ph_sink* sink, void* ctx) {
+    if (!s || !ctx) return PB_ERR_INVALID;
+    g_err.clear();
+    return upload_scene(s->scene, sink ? *sink : g_default_sink, ctx, g_err);
+}
+
+PH_API int ph_run_path_tracer(const char* xml_path, int device, uint32_t frames, float* final_rgba, float* albedo_rgb,
+                              float* normal_rgb, uint32_t* out_w, uint32_t* out_h) {
+    using namespace Pupil;
+    g_err.clear();
+    System system;
+    system.Init(false);
+    pt::B200PTPass pass(&system, device);
+    if (!pass.ok()) { g_err = pass.error(); return PB_ERR_NO_DEVICE; }
+    system.AddPass(&pass);
+    if (!system.SetScene(xml_path) || !pass.ok()) { g_err = system.last_error.empty() ? pass.error() : system.last_error; return PB_ERR_INVALID; }
+    system.RunFrames(frames);
+    if (!pass.ok()) { g_err = pass.error(); return PB_ERR_CUDA; }
+    const uint32_t w = static_cast<uint32_t>(system.world.scene->film_w), h = static_cast<uint32_t>(system.world.scene->film_h);
+    if (out_w) *out_w = w;
+    if (out_h) *out_h = h;
+    auto fetch = [&](const char* name, float* dst, size_t bytes) {
+        if (!dst) return true;
+        Buffer* b = system.buffers.GetBuffer(name);
+        return b && cudaMemcpy(dst, b->cuda_ptr, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
+    };
+    const size_t n = static_cast<size_t>(w) * h;
+    if (!fetch("final result", final_rgba, n * 16) || !fetch("albedo", albedo_rgb, n * 12) || !fetch("normal", normal_rgb, n * 12)) {
+        g_err = "reading back the output buffers failed";
+        return PB_ERR_CUDA;
+    }
+    system.Destroy();
+    return PB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,43 @@
+"""-m gpu: the C++ host layer end to end — headless System + B200PTPass (libpupil_host.so) loads a
+mitsuba-style XML, uploads it through the C ABI, renders N frames (1 frame = 1 spp) on cuda:0 and hands
+back the "final result" / "albedo" / "normal" buffers; compared with the oracle rendering the same XML."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+from pupiloptixlab_b200 import capi, hostlib
+
+pytestmark = pytest.mark.gpu
+DATA = os.path.join(os.path.dirname(__file__), "data")
+
+
+@pytest.mark.parametrize("xml,frames", [("cornell_box.xml", 4), ("cornell_materials.xml", 3)])
+def test_headless_pass_matches_oracle(oracle_api, xml, frames):
+    path = os.path.join(DATA, xml)
+    fin, alb, nrm = hostlib.run_path_tracer(path, frames)
+    sc = hostlib.Scene(path=path)
+    i = sc.info()
+    o = pyoracle.OracleContext(oracle_api)
+    sc.upload(o)
+    so, ao, no = o.render(i.film_w, i.film_h, i.max_depth, 0, frames)
+    mean = so[..., :3] / so[..., 3:4]
+    assert (fin[..., 3] == 1).all()
+    err = np.abs(fin[..., :3] - mean) / (np.abs(mean) + 1e-3)
+    assert (err.max(-1) <= 1e-3).mean() >= 0.998
+    assert (np.abs(alb - ao).max(-1) <= 1e-3).mean() >= 0.998
+    assert (np.abs(nrm - no).max(-1) <= 1e-3).mean() >= 0.998
+
+
+def test_xml_upload_into_the_product_and_trace(oracle_api):
+    sc = hostlib.Scene(path=os.path.join(DATA, "cornell_materials.xml"))
+    g = capi.Context(capi.load())
+    o = pyoracle.OracleContext(oracle_api)
+    sc.upload(g)
+    sc.upload(o)
+    from tests import util_scenes as U
+    rays = U.random_rays(50000, 3, extent=0.9)
+    rays["oy"] += 1.0
+    hg, ho = g.trace_closest(rays), o.trace_closest(rays)
+    assert np.array_equal(hg["prim"], ho["prim"]) and np.array_equal(hg["t"].view(np.uint32), ho["t"].view(np.uint32))
