@@ -30,7 +30,7 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(src):
         obj = os.path.join(CSRC, src[:-3] + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-ccbin", "/usr/bin/g++", "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("PB_NVCC_EXTRA", "").split(), "-ccbin", "/usr/bin/g++", "-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True, env=env)
         log = r.stdout + r.stderr
         with open(os.path.join(CSRC, src[:-3] + ".ptxas.log"), "w") as f:

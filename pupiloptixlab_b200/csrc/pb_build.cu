@@ -116,7 +116,8 @@ int build_bvh(pb_ctx* c, const PrimRec* d_prims_in, uint32_t n, cudaStream_t s) 
     TempPool tp;
     BuildArrays b{};
     b.prims_in = d_prims_in; b.n = n; b.delta = c->delta; b.scene_lo = c->scene_lo; b.scene_hi = c->scene_hi;
-    b.bottom_max = c->bottom_max;
+    b.leaf_max = c->leaf_max;
+    b.bottom_max = std::min(c->bottom_max, 8u * c->leaf_max);
     if (n > 0x1fffffffu) { c->err = "more than 2^29 primitives"; return PB_ERR_LIMIT; }
     unsigned long long* keys_alt = nullptr;
     uint32_t* order_alt = nullptr;

@@ -36,6 +36,7 @@ struct BuildArrays {
     uint32_t* first; uint32_t* last;      // sorted range of each internal node
     V3* ilo; V3* ihi;                     // internal boxes
     uint32_t* flag;                       // arrival counters
+    uint32_t leaf_max;                    // primitives per leaf slot, 1..3 (kLeafMax)
     uint32_t bottom_max;                  // subtrees with at most this many primitives become ONE wide node (<= 24)
 };
 

@@ -57,7 +57,7 @@ PB_HD void collapse_plan(const BuildArrays& b, const CollapseArrays& c, uint32_t
     } else if (ref_count(b, root) <= b.bottom_max) {
         // bottom node: the whole subtree (a contiguous run of the Morton order) in one wide node,
         // cut into <= 8 runs of ceil(count / 8) <= 3 primitives; no sparse inner nodes below it
-        const uint32_t cnt = ref_count(b, root), first = b.first[root], g = (cnt + 7u) / 8u;
+        const uint32_t cnt = ref_count(b, root), first = b.first[root], g = (cnt + 7u) / 8u;   // g <= leaf_max
         for (uint32_t s0 = 0; s0 < cnt; s0 += g) ch[n++] = range_ref(first + s0, cnt - s0 < g ? cnt - s0 : g);
     } else {
         uint32_t bin[8];
@@ -70,7 +70,7 @@ PB_HD void collapse_plan(const BuildArrays& b, const CollapseArrays& c, uint32_t
                 float best_area = -1.f;
                 for (int k = 0; k < n; ++k) {
                     if (bin[k] & kLeafFlag) continue;
-                    const bool big = ref_count(b, bin[k]) > kLeafMax;
+                    const bool big = ref_count(b, bin[k]) > b.leaf_max;
                     if ((pass == 0) != big) continue;
                     float a = half_area(b.ilo[bin[k]], b.ihi[bin[k]]);
                     if (a > best_area) { best_area = a; best = k; }
@@ -84,7 +84,7 @@ PB_HD void collapse_plan(const BuildArrays& b, const CollapseArrays& c, uint32_t
         for (int k = 0; k < n; ++k) {
             const uint32_t r = bin[k];
             if (r & kLeafFlag) ch[k] = range_ref(r & ~kLeafFlag, 1u);
-            else if (ref_count(b, r) <= kLeafMax) ch[k] = range_ref(b.first[r], ref_count(b, r));
+            else if (ref_count(b, r) <= b.leaf_max) ch[k] = range_ref(b.first[r], ref_count(b, r));
             else ch[k] = r;
         }
     }

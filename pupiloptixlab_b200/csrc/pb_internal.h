@@ -64,6 +64,7 @@ struct pb_ctx {
     unsigned long long* d_counters = nullptr;   // [0] ray fetch cursor, [1..3] visit counters
     pb::Wavefront* wf = nullptr;
     int sm_count = 148;
+    uint32_t leaf_max = 2;               // primitives per leaf slot (PB_LEAF_MAX, 1..3)
     uint32_t bottom_max = 8;             // BVH collapse: subtrees up to this size become one wide node (PB_BOTTOM_MAX)
     uint32_t prim_batch = 8;             // lanes holding primitives before a warp runs its primitive tests (PB_PRIM_BATCH)
     uint32_t refill = 20;                // dynamic-fetch threshold (PB_REFILL overrides, tuning only)

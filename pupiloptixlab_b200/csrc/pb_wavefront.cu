@@ -21,6 +21,9 @@
 namespace pb {
 
 constexpr int kWfThreads = 128;
+#ifndef PB_TRACE_MIN_BLOCKS
+#define PB_TRACE_MIN_BLOCKS 8   // 64 registers per thread
+#endif
 enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_COUNT = 16 };
 enum : uint32_t { F_DEPTH_MASK = 0xffu, F_DELTA = 0x100u };
 
@@ -142,7 +145,7 @@ struct ExtendIO {
 };
 
 template<bool COUNT>
-__global__ void __launch_bounds__(kWfThreads) k_extend(WfState s, WfScene sc, int cur) {
+__global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_extend(WfState s, WfScene sc, int cur) {
     __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
     U2 tail[PB_LOCAL_STACK];
     LaneStack st;
@@ -174,7 +177,7 @@ struct ConnectIO {
 };
 
 template<bool COUNT>
-__global__ void __launch_bounds__(kWfThreads) k_connect(WfState s, WfScene sc) {
+__global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfState s, WfScene sc) {
     __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
     U2 tail[PB_LOCAL_STACK];
     LaneStack st;
@@ -352,10 +355,18 @@ __global__ void k_resolve(const float4* __restrict__ sum, float4* __restrict__ f
 
 
 // ---- host orchestration -------------------------------------------------------------------------------------
+// Paths per wave.  Large waves amortise the tail of every persistent kernel and the ~190 launches of a
+// wave (measured on C4: 8 Mi paths 324, 16 Mi 361, 32 Mi 382, 64 Mi 391 Msamples/s); state is ~190 B per
+// path, so the default 64 Mi paths take ~12.5 GB of the 180 GB and are capped at a quarter of the free
+// memory.  PB_WAVE_PATHS overrides.
 static uint32_t wave_path_target() {
     const char* e = getenv("PB_WAVE_PATHS");
     long v = e ? atol(e) : 0;
-    return v > 0 ? (uint32_t)v : (8u << 20);
+    if (v > 0) return (uint32_t)std::min<long>(v, 0x7fffffffL);
+    size_t free_b = 0, total_b = 0;
+    uint64_t paths = 64ull << 20;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) paths = std::min<uint64_t>(paths, std::max<uint64_t>(free_b / 4 / 192, 1ull << 20));
+    return (uint32_t)paths;
 }
 
 void wavefront_free(pb_ctx* c) {

@@ -28,7 +28,8 @@ struct HS {
 
 extern "C" {
 
-static uint32_t hs_bottom_max = 16;
+static uint32_t hs_bottom_max = 16, hs_leaf_max = 3;
+void hs_set_leaf_max(uint32_t v) { hs_leaf_max = v; }
 void hs_set_bottom_max(uint32_t v) { hs_bottom_max = v; }
 
 HS* hs_create(const float* pos, uint32_t n_vert, const uint32_t* idx, uint32_t n_tri, const float* mesh_M,
@@ -73,7 +74,7 @@ HS* hs_create(const float* pos, uint32_t n_vert, const uint32_t* idx, uint32_t n
     std::vector<unsigned long long> keys(n);
     std::vector<uint32_t> order(n), left(n), right(n), pint(n), pleaf(n), first(n), last(n), flag(n, 0);
     BuildArrays b{h->prims_in.data(), n, h->delta, slo, shi, blo.data(), bhi.data(), keys.data(), order.data(),
-                  left.data(), right.data(), pint.data(), pleaf.data(), first.data(), last.data(), ilo.data(), ihi.data(), flag.data(), hs_bottom_max};
+                  left.data(), right.data(), pint.data(), pleaf.data(), first.data(), last.data(), ilo.data(), ihi.data(), flag.data(), hs_leaf_max, hs_bottom_max < 8u * hs_leaf_max ? hs_bottom_max : 8u * hs_leaf_max};
     for (uint32_t i = 0; i < n; ++i) build_prim(b, i);
     // sort pairs (stands in for cub::DeviceRadixSort)
     std::vector<uint32_t> perm(n);
