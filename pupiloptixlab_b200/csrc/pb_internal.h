@@ -71,7 +71,7 @@ struct pb_ctx {
     pb_stats stats{};
 
     pb::TraceScene trace_scene() const {
-        return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill, prim_batch};
+        return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill, prim_batch, 0x47000000u};
     }
 };
 

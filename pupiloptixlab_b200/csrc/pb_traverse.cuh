@@ -29,6 +29,7 @@ struct TraceScene {
     uint32_t n_nodes;
     uint32_t refill;      // refill idle lanes when fewer than this many lanes of a warp hold a ray
     uint32_t prim_batch;  // run the primitive tests once this many lanes of a warp hold primitives
+    uint32_t k47;         // 0x47000000 (see byte_f)
 };
 
 struct Hit { float t, u, v; uint32_t prim; uint32_t obj; };
@@ -74,17 +75,27 @@ struct LaneStack {
     }
 };
 
-// byte j of w as an exact float: 0x4B0000bb is 2^23 + bb, minus 2^23 (one PRMT + one FADD instead
-// of the quarter-rate I2F.U8 the compiler emits for (float)(w >> 8j & 255))
+// Quantised plane byte -> float without a conversion instruction: one PRMT drops byte J of w into
+// byte 1 of 0x47000000, giving the float 32768 + q exactly; the bias is folded into the plane offset
+// (b' = b - 32768 a, rounded DOWN for near planes and UP for far planes, so the node box only ever
+// grows, by at most a * 2^-8 = 0.4 % of one quantisation step).  q in byte 0 would need a bias of
+// 2^23 (half a step of rounding error: not acceptable), and the compiler's own (float)(w >> 8J & 255)
+// is a quarter-rate I2F.U8.  The constant 0x47000000 arrives as a kernel parameter (TraceScene::k47) so
+// that it sits in a register and the selector is the PRMT immediate; as a literal, ptxas makes the
+// constant the immediate and re-materialises the selector with one extra move per PRMT (measured).
 #if defined(__CUDA_ARCH__)
-template<int J> PB_D float byte_f(uint32_t w) { return __fsub_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u + J)), 8388608.0f); }
+template<int J> PB_D float byte_f(uint32_t w, uint32_t k47) { return __uint_as_float(__byte_perm(w, k47, 0x7404u | (J << 4))); }
+PB_D float bias_lo(float a, float b) { return __fmaf_rd(-32768.0f, a, b); }
+PB_D float bias_hi(float a, float b) { return __fmaf_ru(-32768.0f, a, b); }
 #else
-template<int J> inline float byte_f(uint32_t w) { return (float)((w >> (8 * J)) & 0xffu); }
+template<int J> inline float byte_f(uint32_t w, uint32_t) { return (float)((w >> (8 * J)) & 0xffu); }
+inline float bias_lo(float, float b) { return b; }
+inline float bias_hi(float, float b) { return b; }
 #endif
 
 // hit mask of one node for this ray: bits 24..31 inner children (octant ordered), bits 0..23 prims
 PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3, const U4& n4, V3 o, const RayPre& pre,
-                         uint32_t octinv, float tmin, float tmax) {
+                         uint32_t octinv, float tmin, float tmax, uint32_t k47) {
     // n0 = px py pz [ex ey ez imask]; n1 = child_base prim_base meta[0..3] meta[4..7]
     // n2 = qlox[0..7] qloy[0..7]; n3 = qloz[0..7] qhix[0..7]; n4 = qhiy[0..7] qhiz[0..7]
     const uint32_t e = n0.w;
@@ -93,6 +104,9 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
     const float bx = f_mul(f_sub(u2f(n0.x), o.x), pre.id.x);
     const float by = f_mul(f_sub(u2f(n0.y), o.y), pre.id.y);
     const float bz = f_mul(f_sub(u2f(n0.z), o.z), pre.id.z);
+    const float bnx = bias_lo(ax, bx), bfx = bias_hi(ax, bx);
+    const float bny = bias_lo(ay, by), bfy = bias_hi(ay, by);
+    const float bnz = bias_lo(az, bz), bfz = bias_hi(az, bz);
     const bool nx = pre.id.x < 0.f, ny = pre.id.y < 0.f, nz = pre.id.z < 0.f;
     const uint32_t octinv4 = octinv * 0x01010101u;
     uint32_t mask = 0;
@@ -111,9 +125,9 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
         const uint32_t qnz = nz ? hz : lz, qfz = nz ? lz : hz;
 #define PB_CHILD(J)                                                                                              \
         {                                                                                                        \
-            const float tnx = f_fma(byte_f<J>(qnx), ax, bx), tfx = f_fma(byte_f<J>(qfx), ax, bx);               \
-            const float tny = f_fma(byte_f<J>(qny), ay, by), tfy = f_fma(byte_f<J>(qfy), ay, by);               \
-            const float tnz = f_fma(byte_f<J>(qnz), az, bz), tfz = f_fma(byte_f<J>(qfz), az, bz);               \
+            const float tnx = f_fma(byte_f<J>(qnx, k47), ax, bnx), tfx = f_fma(byte_f<J>(qfx, k47), ax, bfx);   \
+            const float tny = f_fma(byte_f<J>(qny, k47), ay, bny), tfy = f_fma(byte_f<J>(qfy, k47), ay, bfy);   \
+            const float tnz = f_fma(byte_f<J>(qnz, k47), az, bnz), tfz = f_fma(byte_f<J>(qfz, k47), az, bfz);   \
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                           \
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                           \
             const uint32_t bits = ((child_bits4 >> (8 * J)) & 0xffu) << ((bit_index4 >> (8 * J)) & 0xffu);      \
@@ -166,7 +180,7 @@ struct Traversal {
             const U4* np = sc.nodes + 5ull * (G.x + rel);
             const U4 n0 = ld_u4(np), n1 = ld_u4(np + 1), n2 = ld_u4(np + 2), n3 = ld_u4(np + 3), n4 = ld_u4(np + 4);
             if (COUNT) cnt->nodes++;
-            const uint32_t hits = node_hits(n0, n1, n2, n3, n4, o, pre, octinv, tmin, best.t);
+            const uint32_t hits = node_hits(n0, n1, n2, n3, n4, o, pre, octinv, tmin, best.t, sc.k47);
             G.x = n1.x;
             G.y = (hits & 0xff000000u) | (n0.w >> 24);
             P.x = n1.y;

@@ -21,6 +21,9 @@
 namespace pb {
 
 constexpr int kWfThreads = 128;
+#ifndef PB_SHADE_MIN_BLOCKS
+#define PB_SHADE_MIN_BLOCKS 5
+#endif
 #ifndef PB_TRACE_MIN_BLOCKS
 #define PB_TRACE_MIN_BLOCKS 8   // 64 registers per thread
 #endif
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfS
 
 // ---- shade<MAT>: one path vertex.  Follows main.cu:84-183 line by line -----------------------------------
 template<int MAT>
-__global__ void __launch_bounds__(kWfThreads) k_shade(WfState s, WfScene sc, int cur, uint32_t k_aov, float* albedo, float* normal) {
+__global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfState s, WfScene sc, int cur, uint32_t k_aov, float* albedo, float* normal) {
     const uint32_t n = s.cnt[C_MAT0 + MAT];
     const uint32_t* q = s.q_mat + (size_t)MAT * s.cap;
     uint32_t* qnext = cur ? s.q_ext[0] : s.q_ext[1];
