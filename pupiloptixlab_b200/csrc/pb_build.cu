@@ -29,6 +29,11 @@ __global__ void k_make_prims(SceneGeom g, PrimRec* out, uint32_t* box /* lo xyz,
     }
 }
 
+__global__ void k_make_trishade(SceneGeom g, float* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < g.n_prims) make_trishade(g, i, out);
+}
+
 __global__ void k_build_prim(BuildArrays b) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < b.n) build_prim(b, i);
@@ -77,8 +82,14 @@ int make_world_prims(pb_ctx* c, PrimRec* d_out, cudaStream_t s) {
     PB_CUDA_TRY(c, cudaMalloc(&d_box, 6 * sizeof(uint32_t)));
     const uint32_t init[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
     PB_CUDA_TRY(c, cudaMemcpyAsync(d_box, init, sizeof(init), cudaMemcpyHostToDevice, s));
-    SceneGeom g{c->d_pos, c->d_nrm, c->d_uv, c->d_idx, c->d_objs, (uint32_t)c->h_objs.size(), n};
+    SceneGeom g{c->d_pos, c->d_nrm, c->d_uv, c->d_idx, c->d_objs, (uint32_t)c->h_objs.size(), n, nullptr};
     k_make_prims<<<blocks_for(n), 256, 0, s>>>(g, d_out, d_box);
+    // per-triangle shading records (pb_scene.cuh)
+    cudaFree(c->d_trishade); c->d_trishade = nullptr;
+    const size_t n_tri_total = c->h_idx.size() / 3;
+    PB_CUDA_TRY(c, cudaMalloc(&c->d_trishade, std::max<size_t>(n_tri_total, 1) * kTriShadeFloats * sizeof(float)));
+    k_make_trishade<<<blocks_for(n), 256, 0, s>>>(g, c->d_trishade);
+    c->stats.kernel_launches += 1;
     uint32_t box[6];
     PB_CUDA_TRY(c, cudaMemcpyAsync(box, d_box, sizeof(box), cudaMemcpyDeviceToHost, s));
     PB_CUDA_TRY(c, cudaStreamSynchronize(s));

@@ -39,6 +39,7 @@ PB_API int pb_create(pb_ctx** out, int device) {
 }
 
 static void free_device_scene(pb_ctx* c) {
+    cudaFree(c->d_trishade); c->d_trishade = nullptr;
     cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_idx);
     cudaFree(c->d_objs); cudaFree(c->d_mats); cudaFree(c->d_emit); cudaFree(c->d_emit_prefix); cudaFree(c->d_env_tables);
     cudaFree(c->d_nodes); cudaFree(c->d_prims);

@@ -25,26 +25,27 @@ PB_HD LocalGeo hit_geometry(const SceneGeom& g, const ObjRec& o, uint32_t prim, 
     LocalGeo r;
     r.texcoord = v2(0.f, 0.f);   // normalised: the reference leaves it stale for meshes without uvs
     if (!(o.flags & OBJ_SPHERE)) {
-        const uint32_t* tri = g.idx + 3ull * (o.index_offset + (prim - o.prim_offset));
-        const uint32_t i0 = tri[0], i1 = tri[1], i2 = tri[2];
-        const float* P = g.pos + 3ull * o.vert_offset;
-        const V3 p0 = {P[3 * i0], P[3 * i0 + 1], P[3 * i0 + 2]}, p1 = {P[3 * i1], P[3 * i1 + 1], P[3 * i1 + 2]},
-                 p2 = {P[3 * i2], P[3 * i2 + 1], P[3 * i2 + 2]};
+        const float* T = g.tri + (size_t)kTriShadeFloats * (o.index_offset + (prim - o.prim_offset));
+        float f[24];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(T) + k);
+            f[4 * k] = v.x; f[4 * k + 1] = v.y; f[4 * k + 2] = v.z; f[4 * k + 3] = v.w;
+        }
+#else
+        for (int k = 0; k < 24; ++k) f[k] = T[k];
+#endif
+        const V3 p0 = {f[0], f[1], f[2]}, p1 = {f[3], f[4], f[5]}, p2 = {f[6], f[7], f[8]};
         const float w = 1.f - bu - bv;
         r.position = xform_point(o.M, w * p0 + bu * p1 + bv * p2);
         V3 n;
-        if (o.flags & OBJ_HAS_NORMALS) {
-            const float* N = g.nrm + 3ull * o.vert_offset;
-            n = w * v3(N[3 * i0], N[3 * i0 + 1], N[3 * i0 + 2]) + bu * v3(N[3 * i1], N[3 * i1 + 1], N[3 * i1 + 2]) +
-                bv * v3(N[3 * i2], N[3 * i2 + 1], N[3 * i2 + 2]);
-        } else {
-            n = cross(p1 - p0, p2 - p0);
-        }
+        if (o.flags & OBJ_HAS_NORMALS) n = w * v3(f[9], f[10], f[11]) + bu * v3(f[12], f[13], f[14]) + bv * v3(f[15], f[16], f[17]);
+        else n = cross(p1 - p0, p2 - p0);
         r.normal = normalize(xform_normal(o.Minv, n));
         if (o.flags & OBJ_FLIP_NORMALS) r.normal *= -1.f;
         if (o.flags & OBJ_HAS_UV) {
-            const float* T = g.uv + 2ull * o.vert_offset;
-            r.texcoord = w * v2(T[2 * i0], T[2 * i0 + 1]) + bu * v2(T[2 * i1], T[2 * i1 + 1]) + bv * v2(T[2 * i2], T[2 * i2 + 1]);
+            r.texcoord = w * v2(f[18], f[19]) + bu * v2(f[20], f[21]) + bv * v2(f[22], f[23]);
             if (o.flags & OBJ_FLIP_TEX) r.texcoord.y = 1.f - r.texcoord.y;
         }
     } else {

@@ -42,6 +42,7 @@ struct pb_ctx {
 
     // ---- device scene
     float* d_pos = nullptr; float* d_nrm = nullptr; float* d_uv = nullptr; uint32_t* d_idx = nullptr;
+    float* d_trishade = nullptr;         // 24 floats per triangle (pb_scene.cuh)
     pb::ObjRec* d_objs = nullptr;
     pb::MatRec* d_mats = nullptr;
     pb::EmitRec* d_emit = nullptr;       // area emitters, then (optionally) the env emitter

@@ -29,15 +29,18 @@ constexpr int kWfThreads = 128;
 #endif
 enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_COUNT = 16 };
 enum : uint32_t { F_DEPTH_MASK = 0xffu, F_DELTA = 0x100u };
+constexpr float kRayTmin = 0.001f, kRayTmax = 1e16f;
+enum { R_ORG = 0, R_DIR = 1, R_HIT = 2, R_OBJ = 3, R_THR = 4, R_RAD = 5, R_COUNT = 6 };
 
 struct WfState {
-    // per path slot
-    float4* ray;        // 2 per slot: (o.xyz, tmin) (d.xyz, tmax)
-    float4* hit;        // (t, u, v, prim bits)
-    uint32_t* hit_obj;
-    float4* thr;        // throughput.xyz, pdf of the BSDF sample that produced the current ray
-    float4* rad;        // radiance.xyz, rng state bits
-    uint32_t* flags;    // depth | F_DELTA
+    // per path slot: one 96-byte record = 3 whole 32-byte sectors (slots are visited in queue order,
+    // i.e. at random, so every access costs whole sectors; six separate SoA arrays cost 6 sectors for 88
+    // useful bytes and two partial-sector writes, measured 590 B of DRAM traffic per shaded vertex)
+    //   [0] o.xyz, depth|flags   [1] d.xyz, -          written by generate / shade
+    //   [2] t, u, v, prim        [3] object, -, -, -   written by extend
+    //   [4] throughput.xyz, pdf of the BSDF sample that produced the ray   [5] radiance.xyz, rng state
+    // tmin / tmax of path rays are the constants of main.cu:77-82,158-163 and are not stored.
+    float4* rec;
     // queues
     uint32_t* q_ext[2];
     uint32_t* q_mat;    // 8 queues of `cap` entries: 0 = miss, 1..7 = material type
@@ -106,11 +109,11 @@ __global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_
     d = normalize(d);
     const float* w = sc.cam.c2w;
     const V3 dir = normalize(v3(dot(V4{w[0], w[1], w[2], w[3]}, d), dot(V4{w[4], w[5], w[6], w[7]}, d), dot(V4{w[8], w[9], w[10], w[11]}, d)));
-    s.ray[2 * slot] = make_float4(w[3], w[7], w[11], 0.001f);
-    s.ray[2 * slot + 1] = make_float4(dir.x, dir.y, dir.z, 1e16f);
-    s.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-    s.rad[slot] = make_float4(0.f, 0.f, 0.f, __uint_as_float(rng.s));
-    s.flags[slot] = 0u;
+    float4* rec = s.rec + (size_t)R_COUNT * slot;
+    rec[R_ORG] = make_float4(w[3], w[7], w[11], __uint_as_float(0u));
+    rec[R_DIR] = make_float4(dir.x, dir.y, dir.z, 0.f);
+    rec[R_THR] = make_float4(1.f, 1.f, 1.f, 0.f);
+    rec[R_RAD] = make_float4(0.f, 0.f, 0.f, __uint_as_float(rng.s));
     s.q_ext[0][slot] = slot;
 }
 
@@ -123,13 +126,15 @@ struct ExtendIO {
     uint32_t slot, pend_slot, pend_bin;   // per lane: current path, finished path waiting for its queue slot
     __device__ __forceinline__ bool load(uint32_t i, V3& o, V3& d, float& tmin, float& tmax) {
         slot = q[i];
-        const float4 a = s.ray[2 * slot], b = s.ray[2 * slot + 1];
-        o = {a.x, a.y, a.z}; d = {b.x, b.y, b.z}; tmin = a.w; tmax = b.w;
+        const float4* rec = s.rec + (size_t)R_COUNT * slot;
+        const float4 a = rec[R_ORG], b = rec[R_DIR];
+        o = {a.x, a.y, a.z}; d = {b.x, b.y, b.z}; tmin = kRayTmin; tmax = kRayTmax;
         return true;
     }
     __device__ __forceinline__ void store(uint32_t, const Hit& h) {
-        s.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-        s.hit_obj[slot] = h.obj;
+        float4* rec = s.rec + (size_t)R_COUNT * slot;
+        rec[R_HIT] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+        rec[R_OBJ] = make_float4(__uint_as_float(h.obj), 0.f, 0.f, 0.f);
         pend_slot = slot;
         pend_bin = h.prim == 0xFFFFFFFFu ? 0u : mats[objs[h.obj].material].type;
     }
@@ -172,9 +177,10 @@ struct ConnectIO {
         if (h.prim != 0xFFFFFFFFu) return;
         const float4 c = s.sh_con[i];
         const uint32_t slot = __float_as_uint(c.w);
-        float4 r = s.rad[slot];
+        float4* rad = s.rec + (size_t)R_COUNT * slot + R_RAD;
+        float4 r = *rad;
         r.x += c.x; r.y += c.y; r.z += c.z;   // one shadow ray per path per bounce: no race
-        s.rad[slot] = r;
+        *rad = r;
     }
     __device__ __forceinline__ void flush() const {}
 };
@@ -210,19 +216,20 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
         float sh_tmax = 0.f;
         if (i < n) {
             slot = q[i];
-            const float4 ro4 = s.ray[2 * slot], rd4 = s.ray[2 * slot + 1], h4 = s.hit[slot];
+            float4* rec = s.rec + (size_t)R_COUNT * slot;
+            const float4 ro4 = rec[R_ORG], rd4 = rec[R_DIR], h4 = rec[R_HIT];
             const V3 ray_o = {ro4.x, ro4.y, ro4.z}, ray_d = {rd4.x, rd4.y, rd4.z};
             const uint32_t prim = __float_as_uint(h4.w);
-            const ObjRec& o = sc.geom.objs[s.hit_obj[slot]];
+            const ObjRec& o = sc.geom.objs[__float_as_uint(rec[R_OBJ].x)];
             const MatRec& m = sc.mats[o.material];
             const LocalGeo geo = hit_geometry(sc.geom, o, prim, h4.x, h4.y, h4.z, ray_o, ray_d, m.twosided != 0u);
             const BsdfLocal bsdf = bsdf_local<MAT>(m, geo.texcoord);
             const int emitter_index = o.emitter_offset >= 0 ? o.emitter_offset + (int)(prim - o.prim_offset) : -1;
-            const float4 t4 = s.thr[slot];
-            float4 r4 = s.rad[slot];
+            const float4 t4 = rec[R_THR];
+            float4 r4 = rec[R_RAD];
             V3 throughput = {t4.x, t4.y, t4.z}, radiance = {r4.x, r4.y, r4.z};
             Rng rng; rng.s = __float_as_uint(r4.w);
-            const uint32_t fl = s.flags[slot];
+            const uint32_t fl = __float_as_uint(ro4.w);
             int depth = (int)(fl & F_DEPTH_MASK);
             if (depth == 0) {  // primary hit: main.cu:87-101
                 if (emitter_index >= 0) radiance += emitter_radiance(sc.em.rec[emitter_index], geo.texcoord);
@@ -283,15 +290,15 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
                     } else {
                         throughput *= br.f * fabsf(br.wi.z) / br.pdf;
                         const V3 nd = to_world(br.wi, geo.normal);
-                        s.ray[2 * slot] = make_float4(geo.position.x, geo.position.y, geo.position.z, 0.001f);
-                        s.ray[2 * slot + 1] = make_float4(nd.x, nd.y, nd.z, 1e16f);
-                        s.thr[slot] = make_float4(throughput.x, throughput.y, throughput.z, br.pdf);
-                        s.flags[slot] = (uint32_t)depth | ((br.lobe & LOBE_DELTA) ? F_DELTA : 0u);
+                        rec[R_ORG] = make_float4(geo.position.x, geo.position.y, geo.position.z,
+                                                 __uint_as_float((uint32_t)depth | ((br.lobe & LOBE_DELTA) ? F_DELTA : 0u)));
+                        rec[R_DIR] = make_float4(nd.x, nd.y, nd.z, 0.f);
+                        rec[R_THR] = make_float4(throughput.x, throughput.y, throughput.z, br.pdf);
                         push_ray = true;
                     }
                 }
             }
-            s.rad[slot] = make_float4(radiance.x, radiance.y, radiance.z, __uint_as_float(rng.s));
+            rec[R_RAD] = make_float4(radiance.x, radiance.y, radiance.z, __uint_as_float(rng.s));
         }
         const uint32_t pr = warp_append(next_count, push_ray);
         if (push_ray) qnext[pr] = slot;
@@ -310,7 +317,9 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
     const EmitRec& env = sc.em.rec[sc.em.n_area];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t slot = s.q_mat[i];
-        const uint32_t fl = s.flags[slot];
+        float4* rec = s.rec + (size_t)R_COUNT * slot;
+        const float4 ro4 = rec[R_ORG];
+        const uint32_t fl = __float_as_uint(ro4.w);
         const bool primary = (fl & F_DEPTH_MASK) == 0u;
         if (primary) {
             const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
@@ -320,19 +329,19 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
             }
         }
         if (env.type == EM_NONE) continue;
-        const float4 ro4 = s.ray[2 * slot], rd4 = s.ray[2 * slot + 1];
+        const float4 rd4 = rec[R_DIR];
         const V3 ray_o = {ro4.x, ro4.y, ro4.z}, rd = normalize(v3(rd4.x, rd4.y, rd4.z));
         EmitEval ev;
         emitter_eval(env, ev, ray_o + rd, v3(0.f), v2(0.f, 0.f), ray_o);
         V3 env_radiance = ev.radiance;
-        float4 r4 = s.rad[slot];
+        float4 r4 = rec[R_RAD];
         if (!primary) {
-            const float4 t4 = s.thr[slot];
+            const float4 t4 = rec[R_THR];
             const float mis = mis_weight(t4.w, ev.pdf);
             env_radiance *= v3(t4.x, t4.y, t4.z) * mis;
         }
         r4.x += env_radiance.x; r4.y += env_radiance.y; r4.z += env_radiance.z;
-        s.rad[slot] = r4;
+        rec[R_RAD] = r4;
     }
 }
 
@@ -342,7 +351,7 @@ __global__ void __launch_bounds__(256) k_accumulate(WfState s, float4* sum, uint
     if (pixel >= n_px) return;
     float4 a = sum[pixel];
     for (uint32_t k = 0; k < k_count; ++k) {
-        const float4 r = s.rad[(size_t)k * n_px + pixel];
+        const float4 r = s.rec[(size_t)R_COUNT * ((size_t)k * n_px + pixel) + R_RAD];
         a.x += r.x; a.y += r.y; a.z += r.z; a.w += 1.f;
     }
     sum[pixel] = a;
@@ -387,14 +396,12 @@ static int wavefront_reserve(pb_ctx* c, uint32_t cap) {
     const size_t n = cap;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += al(bytes); return o; };
-    const size_t o_ray = take(n * 32), o_hit = take(n * 16), o_obj = take(n * 4), o_thr = take(n * 16), o_rad = take(n * 16),
-                 o_flags = take(n * 4), o_q0 = take(n * 4), o_q1 = take(n * 4), o_qm = take(n * 4 * 8), o_shr = take(n * 32),
+    const size_t o_rec = take(n * 16 * R_COUNT), o_q0 = take(n * 4), o_q1 = take(n * 4), o_qm = take(n * 4 * 8), o_shr = take(n * 32),
                  o_shc = take(n * 16), o_cnt = take(C_COUNT * 4), o_tot = take(64);
     PB_CUDA_TRY(c, cudaMalloc(&c->wf->block, off));
     char* b = static_cast<char*>(c->wf->block);
     WfState& s = c->wf->st;
-    s.ray = (float4*)(b + o_ray); s.hit = (float4*)(b + o_hit); s.hit_obj = (uint32_t*)(b + o_obj);
-    s.thr = (float4*)(b + o_thr); s.rad = (float4*)(b + o_rad); s.flags = (uint32_t*)(b + o_flags);
+    s.rec = (float4*)(b + o_rec);
     s.q_ext[0] = (uint32_t*)(b + o_q0); s.q_ext[1] = (uint32_t*)(b + o_q1); s.q_mat = (uint32_t*)(b + o_qm);
     s.sh_ray = (float4*)(b + o_shr); s.sh_con = (float4*)(b + o_shc);
     s.cnt = (uint32_t*)(b + o_cnt); s.totals = (unsigned long long*)(b + o_tot);
@@ -421,7 +428,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     const WfState& st = c->wf->st;
     WfScene sc{};
     sc.ts = c->trace_scene();
-    sc.geom = SceneGeom{c->d_pos, c->d_nrm, c->d_uv, c->d_idx, c->d_objs, (uint32_t)c->h_objs.size(), c->n_prims};
+    sc.geom = SceneGeom{c->d_pos, c->d_nrm, c->d_uv, c->d_idx, c->d_objs, (uint32_t)c->h_objs.size(), c->n_prims, c->d_trishade};
     sc.mats = c->d_mats;
     sc.em = EmitterTable{c->d_emit, c->d_emit_prefix, c->n_area_emitters};
     sc.cam = c->cam;

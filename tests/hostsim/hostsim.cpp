@@ -55,7 +55,7 @@ HS* hs_create(const float* pos, uint32_t n_vert, const uint32_t* idx, uint32_t n
         prim += 1;
     }
     const uint32_t n = prim;
-    SceneGeom g{h->pos.data(), nullptr, nullptr, h->idx.data(), h->objs.data(), (uint32_t)h->objs.size(), n};
+    SceneGeom g{h->pos.data(), nullptr, nullptr, h->idx.data(), h->objs.data(), (uint32_t)h->objs.size(), n, nullptr};
     h->prims_in.resize(n);
     const float fm = 3.402823466e38f;
     V3 slo = v3(fm), shi = v3(-fm);
