@@ -83,12 +83,26 @@ struct LaneStack {
 // is a quarter-rate I2F.U8.  The constant 0x47000000 arrives as a kernel parameter (TraceScene::k47) so
 // that it sits in a register and the selector is the PRMT immediate; as a literal, ptxas makes the
 // constant the immediate and re-materialises the selector with one extra move per PRMT (measured).
-#if defined(__CUDA_ARCH__)
+// PB_BYTE_DP4A (default): the same bytes through the dot-product unit instead.  IDP.4A.U8.U8 (w, 128 << 8J, k47)
+// = 0x47000000 + 128 q = the float 32768 + q / 2, so the plane scale is doubled (plane_scale) and the folded
+// bias is 65536 a (error a * 2^-7, still < 1 % of a step).  IDP issues on the FMA-heavy pipe, which the node
+// test leaves idle (ncu v6: ALU 60 % busy, FMA 22 %); 48 PRMT per node were 30 % of the node test's ALU work.
+#ifndef PB_BYTE_DP4A
+#define PB_BYTE_DP4A 1
+#endif
+#if defined(__CUDA_ARCH__) && PB_BYTE_DP4A
+template<int J> PB_D float byte_f(uint32_t w, uint32_t k47) { return __uint_as_float(__dp4a(w, 128u << (8 * J), k47)); }
+PB_D float plane_scale(float s) { return __fmul_rn(s, 2.0f); }
+PB_D float bias_lo(float a, float b) { return __fmaf_rd(-32768.0f, a, b); }
+PB_D float bias_hi(float a, float b) { return __fmaf_ru(-32768.0f, a, b); }
+#elif defined(__CUDA_ARCH__)
 template<int J> PB_D float byte_f(uint32_t w, uint32_t k47) { return __uint_as_float(__byte_perm(w, k47, 0x7404u | (J << 4))); }
+PB_D float plane_scale(float s) { return s; }
 PB_D float bias_lo(float a, float b) { return __fmaf_rd(-32768.0f, a, b); }
 PB_D float bias_hi(float a, float b) { return __fmaf_ru(-32768.0f, a, b); }
 #else
 template<int J> inline float byte_f(uint32_t w, uint32_t) { return (float)((w >> (8 * J)) & 0xffu); }
+inline float plane_scale(float s) { return s; }
 inline float bias_lo(float, float b) { return b; }
 inline float bias_hi(float, float b) { return b; }
 #endif
@@ -100,7 +114,7 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
     // n2 = qlox[0..7] qloy[0..7]; n3 = qloz[0..7] qhix[0..7]; n4 = qhiy[0..7] qhiz[0..7]
     const uint32_t e = n0.w;
     const float sx = u2f((e & 0xffu) << 23), sy = u2f(((e >> 8) & 0xffu) << 23), sz = u2f(((e >> 16) & 0xffu) << 23);
-    const float ax = f_mul(sx, pre.id.x), ay = f_mul(sy, pre.id.y), az = f_mul(sz, pre.id.z);
+    const float ax = f_mul(plane_scale(sx), pre.id.x), ay = f_mul(plane_scale(sy), pre.id.y), az = f_mul(plane_scale(sz), pre.id.z);
     const float bx = f_mul(f_sub(u2f(n0.x), o.x), pre.id.x);
     const float by = f_mul(f_sub(u2f(n0.y), o.y), pre.id.y);
     const float bz = f_mul(f_sub(u2f(n0.z), o.z), pre.id.z);
