@@ -215,14 +215,14 @@ def product_main(args):
     clocks = ClockSampler(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     rays_c = rays_a = launches = 0
-    ext_ms = con_ms = 0.0
+    ext_ms = con_ms = shd_ms = 0.0
     ext_l = con_l = 0
     per_step_rays_c = []
     e0.record(stream)
     for i in range(args.steps):
         st = dev_step(args.warmup + i)
         rays_c += st["rays_closest"]; rays_a += st["rays_any"]; launches += st["kernel_launches"] + (1 if rank == 0 else 0)
-        ext_ms += st["extend_ms"]; con_ms += st["connect_ms"]; ext_l += st["extend_launches"]; con_l += st["connect_launches"]
+        ext_ms += st["extend_ms"]; con_ms += st["connect_ms"]; shd_ms += st["shade_ms"]; ext_l += st["extend_launches"]; con_l += st["connect_launches"]
         per_step_rays_c.append(st["rays_closest"])
     e1.record(stream)
     barrier()
@@ -303,6 +303,7 @@ def product_main(args):
                                      "unit": "GB/s", "frac": ach_any / peak, "bytes_per_ray": b_any,
                                      "avg_launch_ms": con_ms / max(1, con_l), "launches": con_l,
                                      "share_of_step": con_ms / ms if N == 1 else None}
+        extra["shade_share_of_step"] = shd_ms / ms if N == 1 else None
         extra["mrays_per_s_closest_kernel"] = rays_c / (ext_ms * 1e-3) / 1e6 if ext_ms > 0 else None
         extra["mrays_per_s_any_kernel"] = rays_a / (con_ms * 1e-3) / 1e6 if con_ms > 0 else None
 

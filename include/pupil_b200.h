@@ -132,6 +132,8 @@ typedef struct pb_stats {
     /* PB_RENDER_STAGE_TIMING: summed device time of the traversal launches of the last render    */
     float    extend_ms, connect_ms;
     uint32_t extend_launches, connect_launches;
+    float    shade_ms;                      /* miss + the seven shade launches of every bounce   */
+    uint32_t shade_groups;
 } pb_stats;
 
 typedef struct pb_ctx pb_ctx;

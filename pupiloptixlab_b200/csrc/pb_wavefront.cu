@@ -30,6 +30,30 @@ constexpr int kWfThreads = 128;
 enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_COUNT = 16 };
 enum : uint32_t { F_DEPTH_MASK = 0xffu, F_DELTA = 0x100u };
 constexpr float kRayTmin = 0.001f, kRayTmax = 1e16f;
+// Queue entries are visited in (increasingly random) queue order, so the first touch of a path record is a
+// DRAM round trip that nothing in the warp can overlap.  Every consumer therefore asks L2 for the records
+// of the entries a fixed distance AHEAD of the ones it is about to use (prefetch.global.L2: no register, no
+// scoreboard); kPrefetchAhead entries = a few microseconds of queue progress, far more than the DRAM
+// latency and far less than the time L2 (126 MB) keeps a line under this traffic.
+constexpr uint32_t kPrefetchAhead = 16384u;
+#ifndef PB_TRACE_PREFETCH
+#define PB_TRACE_PREFETCH 1
+#endif
+#ifndef PB_CONNECT_RED
+#define PB_CONNECT_RED 1
+#endif
+// 256-bit accesses to a 32-byte-aligned pair of float4 (sm_100: LDG/STG.E.ENL2.256).  A path record is visited
+// by one lane at a random address, so every request costs the L1 one pass per lane; pairing the two halves of
+// a sector halves the passes (the shade kernels were bound by exactly that: ~570 L1 wavefronts per warp-vertex).
+__device__ __forceinline__ void ld256(const float4* p, float4& a, float4& b) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st256(float4* p, const float4& a, const float4& b) {
+    asm volatile("st.global.v8.f32 [%8], {%0,%1,%2,%3,%4,%5,%6,%7};"
+                 :: "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w), "l"(p) : "memory");
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 enum { R_ORG = 0, R_DIR = 1, R_HIT = 2, R_OBJ = 3, R_THR = 4, R_RAD = 5, R_COUNT = 6 };
 
 struct WfState {
@@ -110,10 +134,8 @@ __global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_
     const float* w = sc.cam.c2w;
     const V3 dir = normalize(v3(dot(V4{w[0], w[1], w[2], w[3]}, d), dot(V4{w[4], w[5], w[6], w[7]}, d), dot(V4{w[8], w[9], w[10], w[11]}, d)));
     float4* rec = s.rec + (size_t)R_COUNT * slot;
-    rec[R_ORG] = make_float4(w[3], w[7], w[11], __uint_as_float(0u));
-    rec[R_DIR] = make_float4(dir.x, dir.y, dir.z, 0.f);
-    rec[R_THR] = make_float4(1.f, 1.f, 1.f, 0.f);
-    rec[R_RAD] = make_float4(0.f, 0.f, 0.f, __uint_as_float(rng.s));
+    st256(rec + R_ORG, make_float4(w[3], w[7], w[11], __uint_as_float(0u)), make_float4(dir.x, dir.y, dir.z, 0.f));
+    st256(rec + R_THR, make_float4(1.f, 1.f, 1.f, 0.f), make_float4(0.f, 0.f, 0.f, __uint_as_float(rng.s)));
     s.q_ext[0][slot] = slot;
 }
 
@@ -123,18 +145,21 @@ struct ExtendIO {
     const ObjRec* __restrict__ objs;
     const MatRec* __restrict__ mats;
     const uint32_t* __restrict__ q;
+    uint32_t n;
     uint32_t slot, pend_slot, pend_bin;   // per lane: current path, finished path waiting for its queue slot
     __device__ __forceinline__ bool load(uint32_t i, V3& o, V3& d, float& tmin, float& tmax) {
         slot = q[i];
+        if (PB_TRACE_PREFETCH && i + 2u * kPrefetchAhead < n) prefetch_l2(q + i + 2u * kPrefetchAhead);
+        if (PB_TRACE_PREFETCH && i + kPrefetchAhead < n) prefetch_l2(s.rec + (size_t)R_COUNT * q[i + kPrefetchAhead]);
         const float4* rec = s.rec + (size_t)R_COUNT * slot;
-        const float4 a = rec[R_ORG], b = rec[R_DIR];
+        float4 a, b;
+        ld256(rec + R_ORG, a, b);
         o = {a.x, a.y, a.z}; d = {b.x, b.y, b.z}; tmin = kRayTmin; tmax = kRayTmax;
         return true;
     }
     __device__ __forceinline__ void store(uint32_t, const Hit& h) {
         float4* rec = s.rec + (size_t)R_COUNT * slot;
-        rec[R_HIT] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-        rec[R_OBJ] = make_float4(__uint_as_float(h.obj), 0.f, 0.f, 0.f);
+        st256(rec + R_HIT, make_float4(h.t, h.u, h.v, __uint_as_float(h.prim)), make_float4(__uint_as_float(h.obj), 0.f, 0.f, 0.f));
         pend_slot = slot;
         pend_bin = h.prim == 0xFFFFFFFFu ? 0u : mats[objs[h.obj].material].type;
     }
@@ -160,7 +185,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_extend(WfSt
     st.init(s_stack + threadIdx.x, kWfThreads, tail);
     const uint32_t n = s.cnt[cur ? C_EXT_B : C_EXT_A];
     TraceCounters tc = {0ull, 0ull, 0ull};
-    ExtendIO io{s, sc.geom.objs, sc.mats, cur ? s.q_ext[1] : s.q_ext[0], 0u, 0u, 8u};
+    ExtendIO io{s, sc.geom.objs, sc.mats, cur ? s.q_ext[1] : s.q_ext[0], n, 0u, 0u, 8u};
     trace_loop<false, COUNT>(sc.ts, io, st, &s.cnt[C_CUR_EXT], n, sc.ts.refill, tc);
     if (COUNT) { atomicAdd(&s.totals[2], tc.nodes); atomicAdd(&s.totals[3], tc.tris); atomicAdd(&s.totals[4], tc.spheres); }
 }
@@ -168,8 +193,11 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_extend(WfSt
 // ---- connect: any hit for the shadow queue; unoccluded contributions go to the path radiance --------
 struct ConnectIO {
     WfState s;
+    uint32_t n;
     __device__ __forceinline__ bool load(uint32_t i, V3& o, V3& d, float& tmin, float& tmax) const {
-        const float4 a = s.sh_ray[2 * i], b = s.sh_ray[2 * i + 1];
+        if (PB_TRACE_PREFETCH && i + kPrefetchAhead < n) { prefetch_l2(s.sh_ray + 2 * (i + kPrefetchAhead)); prefetch_l2(s.sh_con + i + kPrefetchAhead); }
+        float4 a, b;
+        ld256(s.sh_ray + 2 * i, a, b);
         o = {a.x, a.y, a.z}; d = {b.x, b.y, b.z}; tmin = a.w; tmax = b.w;
         return true;
     }
@@ -177,10 +205,14 @@ struct ConnectIO {
         if (h.prim != 0xFFFFFFFFu) return;
         const float4 c = s.sh_con[i];
         const uint32_t slot = __float_as_uint(c.w);
-        float4* rad = s.rec + (size_t)R_COUNT * slot + R_RAD;
-        float4 r = *rad;
-        r.x += c.x; r.y += c.y; r.z += c.z;   // one shadow ray per path per bounce: no race
-        *rad = r;
+        // one shadow ray per path per bounce, so these are plain adds — issued as reductions (RED.ADD.F32, no
+        // return value) so that the finishing lane does not hold its warp for a DRAM round trip of the record
+        float* rad = (float*)(s.rec + (size_t)R_COUNT * slot + R_RAD);
+#if PB_CONNECT_RED
+        atomicAdd(rad, c.x); atomicAdd(rad + 1, c.y); atomicAdd(rad + 2, c.z);
+#else
+        float4 r = *(float4*)rad; r.x += c.x; r.y += c.y; r.z += c.z; *(float4*)rad = r;
+#endif
     }
     __device__ __forceinline__ void flush() const {}
 };
@@ -193,7 +225,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfS
     st.init(s_stack + threadIdx.x, kWfThreads, tail);
     const uint32_t n = s.cnt[C_SHADOW];
     TraceCounters tc = {0ull, 0ull, 0ull};
-    ConnectIO io{s};
+    ConnectIO io{s, n};
     trace_loop<true, COUNT>(sc.ts, io, st, &s.cnt[C_CUR_CON], n, sc.ts.refill, tc);
     if (COUNT) { atomicAdd(&s.totals[5], tc.nodes); atomicAdd(&s.totals[6], tc.tris); atomicAdd(&s.totals[7], tc.spheres); }
 }
@@ -208,6 +240,8 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
     uint32_t* next_count = &s.cnt[cur ? C_EXT_A : C_EXT_B];
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    // (Requesting the next iterations' records from L2 ahead of time was tried and is slower: these kernels are
+    // bound by L1 passes per scattered request, not by exposed latency - profiles/r01_shade.md.)
     for (uint32_t base = warp * 32u; base < n; base += n_warps * 32u) {
         const uint32_t i = base + lane;
         bool push_ray = false, push_shadow = false;
@@ -217,16 +251,17 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
         if (i < n) {
             slot = q[i];
             float4* rec = s.rec + (size_t)R_COUNT * slot;
-            const float4 ro4 = rec[R_ORG], rd4 = rec[R_DIR], h4 = rec[R_HIT];
+            float4 ro4, rd4, h4, ob4, t4, r4;
+            ld256(rec + R_ORG, ro4, rd4);
+            ld256(rec + R_HIT, h4, ob4);
+            ld256(rec + R_THR, t4, r4);
             const V3 ray_o = {ro4.x, ro4.y, ro4.z}, ray_d = {rd4.x, rd4.y, rd4.z};
             const uint32_t prim = __float_as_uint(h4.w);
-            const ObjRec& o = sc.geom.objs[__float_as_uint(rec[R_OBJ].x)];
+            const ObjRec& o = sc.geom.objs[__float_as_uint(ob4.x)];
             const MatRec& m = sc.mats[o.material];
             const LocalGeo geo = hit_geometry(sc.geom, o, prim, h4.x, h4.y, h4.z, ray_o, ray_d, m.twosided != 0u);
             const BsdfLocal bsdf = bsdf_local<MAT>(m, geo.texcoord);
             const int emitter_index = o.emitter_offset >= 0 ? o.emitter_offset + (int)(prim - o.prim_offset) : -1;
-            const float4 t4 = rec[R_THR];
-            float4 r4 = rec[R_RAD];
             V3 throughput = {t4.x, t4.y, t4.z}, radiance = {r4.x, r4.y, r4.z};
             Rng rng; rng.s = __float_as_uint(r4.w);
             const uint32_t fl = __float_as_uint(ro4.w);
@@ -290,22 +325,22 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
                     } else {
                         throughput *= br.f * fabsf(br.wi.z) / br.pdf;
                         const V3 nd = to_world(br.wi, geo.normal);
-                        rec[R_ORG] = make_float4(geo.position.x, geo.position.y, geo.position.z,
-                                                 __uint_as_float((uint32_t)depth | ((br.lobe & LOBE_DELTA) ? F_DELTA : 0u)));
-                        rec[R_DIR] = make_float4(nd.x, nd.y, nd.z, 0.f);
-                        rec[R_THR] = make_float4(throughput.x, throughput.y, throughput.z, br.pdf);
+                        st256(rec + R_ORG, make_float4(geo.position.x, geo.position.y, geo.position.z,
+                                                       __uint_as_float((uint32_t)depth | ((br.lobe & LOBE_DELTA) ? F_DELTA : 0u))),
+                              make_float4(nd.x, nd.y, nd.z, 0.f));
+                        t4 = make_float4(throughput.x, throughput.y, throughput.z, br.pdf);
                         push_ray = true;
                     }
                 }
             }
-            rec[R_RAD] = make_float4(radiance.x, radiance.y, radiance.z, __uint_as_float(rng.s));
+            // throughput|pdf (unchanged for a finished path) and radiance|rng share a sector: one 256-bit store
+            st256(rec + R_THR, t4, make_float4(radiance.x, radiance.y, radiance.z, __uint_as_float(rng.s)));
         }
         const uint32_t pr = warp_append(next_count, push_ray);
         if (push_ray) qnext[pr] = slot;
         const uint32_t ps = warp_append(&s.cnt[C_SHADOW], push_shadow);
         if (push_shadow) {
-            s.sh_ray[2 * ps] = make_float4(sh_o.x, sh_o.y, sh_o.z, 0.001f);
-            s.sh_ray[2 * ps + 1] = make_float4(sh_d.x, sh_d.y, sh_d.z, sh_tmax);
+            st256(s.sh_ray + 2 * ps, make_float4(sh_o.x, sh_o.y, sh_o.z, 0.001f), make_float4(sh_d.x, sh_d.y, sh_d.z, sh_tmax));
             s.sh_con[ps] = make_float4(contrib.x, contrib.y, contrib.z, __uint_as_float(slot));
         }
     }
@@ -318,7 +353,8 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t slot = s.q_mat[i];
         float4* rec = s.rec + (size_t)R_COUNT * slot;
-        const float4 ro4 = rec[R_ORG];
+        float4 ro4, rd4;
+        ld256(rec + R_ORG, ro4, rd4);
         const uint32_t fl = __float_as_uint(ro4.w);
         const bool primary = (fl & F_DEPTH_MASK) == 0u;
         if (primary) {
@@ -329,7 +365,6 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
             }
         }
         if (env.type == EM_NONE) continue;
-        const float4 rd4 = rec[R_DIR];
         const V3 ray_o = {ro4.x, ro4.y, ro4.z}, rd = normalize(v3(rd4.x, rd4.y, rd4.z));
         EmitEval ev;
         emitter_eval(env, ev, ray_o + rd, v3(0.f), v2(0.f, 0.f), ray_o);
@@ -439,7 +474,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     PB_CUDA_TRY(c, cudaEventCreate(&e0)); PB_CUDA_TRY(c, cudaEventCreate(&e1));
     PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 64, s));
     const bool counted = (p->flags & PB_RENDER_COUNTED) != 0u, timing = (p->flags & PB_RENDER_STAGE_TIMING) != 0u;
-    std::vector<cudaEvent_t> ev_ext, ev_con;   // begin/end pairs around every traversal launch
+    std::vector<cudaEvent_t> ev_ext, ev_con, ev_shd;   // begin/end pairs around every traversal launch
     auto mark = [&](std::vector<cudaEvent_t>& v) {
         if (!timing) return;
         cudaEvent_t e;
@@ -462,6 +497,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
             if (counted) k_extend<true><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
             else k_extend<false><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
             mark(ev_ext);
+            mark(ev_shd);
             k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, d_albedo, d_normal);
             launch_shade<1>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
             launch_shade<2>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
@@ -471,6 +507,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
             launch_shade<6>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
             launch_shade<7>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
             k_after_shade<<<1, 1, 0, s>>>(st);
+            mark(ev_shd);
             mark(ev_con);
             if (counted) k_connect<true><<<g_trace, kWfThreads, 0, s>>>(st, sc);
             else k_connect<false><<<g_trace, kWfThreads, 0, s>>>(st, sc);
@@ -502,7 +539,8 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
         return total;
     };
     c->stats.extend_launches = (uint32_t)(ev_ext.size() / 2); c->stats.connect_launches = (uint32_t)(ev_con.size() / 2);
-    c->stats.extend_ms = sum_pairs(ev_ext); c->stats.connect_ms = sum_pairs(ev_con);
+    c->stats.shade_groups = (uint32_t)(ev_shd.size() / 2);
+    c->stats.extend_ms = sum_pairs(ev_ext); c->stats.connect_ms = sum_pairs(ev_con); c->stats.shade_ms = sum_pairs(ev_shd);
     return PB_OK;
 }
 
