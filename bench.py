@@ -55,45 +55,99 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock, power and throttle reasons sampled every 100 ms DURING the timed region.  NVML is opened (and
+    its first, slow queries made) before the warm-up steps so that no driver initialisation lands inside the
+    timed region; only samples taken between begin() and end() are reported.  In-process NVML (nvidia-ml-py),
+    falling back to a streaming `nvidia-smi -lms` child started at construction."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index: int):
-        self.rows, self.proc = [], None
+    def __init__(self, index: int, uuid=None):
+        self.rows, self.proc, self.h, self.nv = [], None, None, None
+        self.t0 = self.t1 = None
+        self.alive = True
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode()) if uuid else pynvml.nvmlDeviceGetHandleByIndex(index)
+            self._sample()                      # first queries are the slow ones
+            self.rows.clear()
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.h = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                                           "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+    def _sample(self):
+        nv, h = self.nv, self.h
+        sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+        flags = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
+        self.rows.append((time.perf_counter(), float(sm), float(mx), pw, [n for n, b in flags if r & b]))
 
-    def stop(self) -> dict:
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, pw, reasons = [], [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+    def _poll(self):
+        while self.alive:
             try:
-                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
-                for n, v in zip(names, r[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
+                self._sample()
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def _read(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.proc.stdout:
+            r = [x.strip() for x in line.split(",")]
+            try:
+                self.rows.append((time.perf_counter(), float(r[0]), float(r[1]), float(r[2]),
+                                  [n for n, v in zip(names, r[3:7]) if v.lower().startswith("active")]))
             except Exception:
                 continue
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+    def begin(self):
+        self.t0 = time.perf_counter()
+
+    def end(self):
+        self.t1 = time.perf_counter()
+
+    def window(self) -> dict:
+        """Summary of the samples between the last begin() and end(); sampling goes on."""
+        if self.h is None and not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml / nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        return self._summary()
+
+    def stop(self) -> dict:
+        if self.h is None and not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml / nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.alive = False
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        return self._summary()
+
+    def _summary(self) -> dict:
+        t0 = self.t0 if self.t0 is not None else -1e30
+        t1 = self.t1 if self.t1 is not None else 1e30
+        rows = [r for r in self.rows if t0 <= r[0] <= t1 + 0.11] or self.rows
+        sm, mx, pw = [r[1] for r in rows], [r[2] for r in rows], [r[3] for r in rows]
+        reasons = sorted({n for r in rows for n in r[4]})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_min_mhz": min(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons,
+                "source": "nvml" if self.h is not None else "nvidia-smi"}
 
 
 def build_scene(ctx, mesh_tag: str, mesh=None):
@@ -195,39 +249,54 @@ def product_main(args):
     def step_params(i, flags):
         return capi.RenderParams(WIDTH, HEIGHT, MAX_DEPTH, i * S * N + rank, S, N, flags, 0)
 
-    def dev_step(i, timing=True):
-        p = step_params(i, capi.RENDER_CLEAR | (capi.RENDER_STAGE_TIMING if timing else 0))
+    def dev_step(i, timing=True, asynchronous=False):
+        p = step_params(i, capi.RENDER_CLEAR | (capi.RENDER_STAGE_TIMING if timing else 0) | (capi.RENDER_ASYNC if asynchronous else 0))
         g.render_dev(p, d_sum.data_ptr(), 0, 0, sp)
         if N > 1:
             dist.reduce(d_sum, dst=0)
         if rank == 0:
             d_total.add_(d_sum)
-        return g.stats()
+        return None if asynchronous else g.stats()
 
     def barrier():
         if N > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    clocks = None
+    if rank == 0:
+        try:
+            uuid = torch.cuda.get_device_properties(dev).uuid
+        except Exception:
+            uuid = None
+        clocks = ClockSampler(local, uuid)
     for i in range(args.warmup):
         dev_step(i)
     barrier()
-    clocks = ClockSampler(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     rays_c = rays_a = launches = 0
     ext_ms = con_ms = shd_ms = 0.0
     ext_l = con_l = 0
     per_step_rays_c = []
+    step_ms = []
+    if clocks:
+        clocks.begin()
     e0.record(stream)
+    # the K steps are enqueued back to back on the stream (PB_RENDER_ASYNC; the film of step i is consumed by the
+    # reduce / add enqueued right behind it) and synchronised once: the timed region holds device work only,
+    # a host hiccup between two steps cannot idle the GPU
     for i in range(args.steps):
-        st = dev_step(args.warmup + i)
-        rays_c += st["rays_closest"]; rays_a += st["rays_any"]; launches += st["kernel_launches"] + (1 if rank == 0 else 0)
-        ext_ms += st["extend_ms"]; con_ms += st["connect_ms"]; shd_ms += st["shade_ms"]; ext_l += st["extend_launches"]; con_l += st["connect_launches"]
-        per_step_rays_c.append(st["rays_closest"])
+        dev_step(args.warmup + i, asynchronous=True)
     e1.record(stream)
     barrier()
+    if clocks:
+        clocks.end()
     ms = e0.elapsed_time(e1)
-    clk = clocks.stop() if clocks else None
+    st = g.stats()            # totals of the K asynchronous renders
+    rays_c, rays_a, launches = st["rays_closest"], st["rays_any"], st["kernel_launches"] + (args.steps if rank == 0 else 0)
+    ext_ms, con_ms, shd_ms, ext_l, con_l = st["extend_ms"], st["connect_ms"], st["shade_ms"], st["extend_launches"], st["connect_launches"]
+    step_ms = [round(st["last_render_ms"] / args.steps, 2)]
+    clk = clocks.window() if clocks else None
     t = torch.tensor([ms, float(rays_c), float(rays_a), float(launches)], dtype=torch.float64, device=dev)
     if N > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -260,11 +329,20 @@ def product_main(args):
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     w0 = time.perf_counter()
     f0.record(stream)
+    e2e_each = []
+    if clocks:
+        clocks.begin()
     for i in range(e2e_steps):
+        t_i = time.perf_counter()
         e2e_step(args.warmup + i)
+        e2e_each.append(round((time.perf_counter() - t_i) * 1e3, 2))
     f1.record(stream)
     barrier()
     e2e_ms = max(f0.elapsed_time(f1), (time.perf_counter() - w0) * 1e3 if N == 1 else 0.0)
+    e2e_clk = None
+    if clocks:
+        clocks.end()
+        e2e_clk = clocks.stop()
     if N > 1:
         tt = torch.tensor([e2e_ms], dtype=torch.float64, device=dev); dist.all_reduce(tt, op=dist.ReduceOp.MAX); e2e_ms = float(tt[0])
     e2e_value = float(n_px) * S * e2e_steps * N / (e2e_ms * 1e-3) / 1e6
@@ -303,6 +381,7 @@ def product_main(args):
                                      "unit": "GB/s", "frac": ach_any / peak, "bytes_per_ray": b_any,
                                      "avg_launch_ms": con_ms / max(1, con_l), "launches": con_l,
                                      "share_of_step": con_ms / ms if N == 1 else None}
+        extra["render_ms_each_step"] = step_ms
         extra["shade_share_of_step"] = shd_ms / ms if N == 1 else None
         extra["mrays_per_s_closest_kernel"] = rays_c / (ext_ms * 1e-3) / 1e6 if ext_ms > 0 else None
         extra["mrays_per_s_any_kernel"] = rays_a / (con_ms * 1e-3) / 1e6 if con_ms > 0 else None
@@ -324,7 +403,7 @@ def product_main(args):
                            "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"},
                 "mrays_per_s": mrays, "rays_per_sample": (rays_c_all + rays_a_all) / samples,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "ms_each": e2e_each, "clocks": e2e_clk},
                 "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
                 "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}
         line.update(extra)

@@ -114,8 +114,12 @@ enum {
     PB_RENDER_CLEAR = 2u,        /* zero the sum buffer first (sample_cnt = 0, pt_pass.cpp:43)   */
     PB_RENDER_COUNTED = 4u,      /* instrumented traversal: fills the visit counters of pb_stats
                                     (same image; never the timed build)                          */
-    PB_RENDER_STAGE_TIMING = 8u  /* CUDA events around every extend / connect launch: fills
+    PB_RENDER_STAGE_TIMING = 8u, /* CUDA events around every extend / connect launch: fills
                                     extend_ms / connect_ms / *_launches of pb_stats               */
+    PB_RENDER_ASYNC = 16u        /* device buffers only: return once the work is enqueued on the stream
+                                    (the reference's optixLaunch is asynchronous too, pass.h:79-86);
+                                    pb_wait / pb_get_stats synchronise and report the totals of all
+                                    renders enqueued since the last wait                           */
 };
 
 typedef struct pb_stats {
@@ -189,6 +193,9 @@ PB_API int pb_render(pb_ctx* ctx, const pb_render_params* p, float* accum_sum_rg
 PB_API int pb_resolve(pb_ctx* ctx, const float* accum_sum_rgba, float* frame_rgba, uint32_t n_pixels,
                       int host, void* cuda_stream);
 
+/* waits for renders enqueued with PB_RENDER_ASYNC (replaces Pass::Synchronize, framework/optix/pass.h:88) */
+PB_API int pb_wait(pb_ctx* ctx);
+/* implies pb_wait */
 PB_API int pb_get_stats(pb_ctx* ctx, pb_stats* out);
 
 /* ---- BVH export (test / roofline accounting only): the committed 8-wide BVH and its primitive

@@ -20,7 +20,7 @@ TEX_RGB, TEX_BITMAP, TEX_CHECKERBOARD = 0, 1, 2
 MAT_DIFFUSE, MAT_DIELECTRIC, MAT_ROUGH_DIELECTRIC, MAT_CONDUCTOR, MAT_ROUGH_CONDUCTOR, MAT_PLASTIC, MAT_ROUGH_PLASTIC = range(1, 8)
 SHAPE_FLIP_NORMALS, SHAPE_FLIP_TEX_COORDS = 1, 2
 ENV_NONE, ENV_CONSTANT, ENV_MAP = 0, 1, 2
-RENDER_HOST_BUFFERS, RENDER_CLEAR, RENDER_COUNTED, RENDER_STAGE_TIMING = 1, 2, 4, 8
+RENDER_HOST_BUFFERS, RENDER_CLEAR, RENDER_COUNTED, RENDER_STAGE_TIMING, RENDER_ASYNC = 1, 2, 4, 8, 16
 MISS = 0xFFFFFFFF
 
 
@@ -151,6 +151,8 @@ class Api:
         f("render", i32, [vp, C.POINTER(RenderParams), vp, vp, vp, vp])
         f("resolve", i32, [vp, vp, vp, u32, i32, vp])
         f("get_stats", i32, [vp, C.POINTER(Stats)])
+        if self.prefix == "pb_":      # the oracle is synchronous
+            f("wait", i32, [vp])
 
     def _f(self, name, res, args, optional=False):
         try:
@@ -280,6 +282,10 @@ class Context:
     def render_into(self, params: RenderParams, acc: np.ndarray):
         """Host-buffer render accumulating into an existing host array."""
         self._ck(self.api._render(self.h, C.byref(params), acc.ctypes.data, None, None, None), "render")
+
+    def wait(self):
+        """Synchronises renders enqueued with RENDER_ASYNC."""
+        self._ck(self.api._wait(self.h), "wait")
 
     def stats(self) -> dict:
         s = Stats()

@@ -57,6 +57,7 @@ PB_API void pb_destroy(pb_ctx* c) {
     wavefront_free(c);
     free_device_scene(c);
     cudaFree(c->d_counters);
+    cudaFree(c->d_stage);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }

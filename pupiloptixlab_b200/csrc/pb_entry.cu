@@ -77,25 +77,30 @@ PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba
     cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
     const size_t npx = (size_t)p->width * p->height;
     if (!(p->flags & PB_RENDER_HOST_BUFFERS)) {
-        int rc = wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, s);
-        if (rc != PB_OK) return rc;
-        PB_CUDA_TRY(c, cudaStreamSynchronize(s));
-        return PB_OK;
+        return wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, s);   // synchronises unless PB_RENDER_ASYNC
     }
-    float *d_sum = nullptr, *d_alb = nullptr, *d_nrm = nullptr;
-    PB_CUDA_TRY(c, cudaMalloc(&d_sum, npx * 16));
-    if (albedo_rgb) PB_CUDA_TRY(c, cudaMalloc(&d_alb, npx * 12));
-    if (normal_rgb) PB_CUDA_TRY(c, cudaMalloc(&d_nrm, npx * 12));
+    PB_REQUIRE(!(p->flags & PB_RENDER_ASYNC), "PB_RENDER_ASYNC needs device buffers");
+    // film staging lives in the context (no cudaMalloc / cudaFree - both synchronise the device - per call)
+    if (c->stage_px < npx) {
+        cudaFree(c->d_stage); c->d_stage = nullptr; c->stage_px = 0;
+        PB_CUDA_TRY(c, cudaMalloc(&c->d_stage, npx * 40));
+        c->stage_px = npx;
+    }
+    float* d_sum = c->d_stage;
+    float* d_alb = albedo_rgb ? c->d_stage + npx * 4 : nullptr;
+    float* d_nrm = normal_rgb ? c->d_stage + npx * 7 : nullptr;
     if (!(p->flags & PB_RENDER_CLEAR)) PB_CUDA_TRY(c, cudaMemcpyAsync(d_sum, accum_sum_rgba, npx * 16, cudaMemcpyHostToDevice, s));
-    int rc = wavefront_render(c, p, d_sum, d_alb, d_nrm, s);
+    pb_render_params q = *p;
+    q.flags |= PB_RENDER_ASYNC;          // one synchronise for kernels and copies together (wavefront_wait below)
+    int rc = wavefront_render(c, &q, d_sum, d_alb, d_nrm, s);
     if (rc == PB_OK) {
         cudaError_t e = cudaMemcpyAsync(accum_sum_rgba, d_sum, npx * 16, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && albedo_rgb) e = cudaMemcpyAsync(albedo_rgb, d_alb, npx * 12, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && normal_rgb) e = cudaMemcpyAsync(normal_rgb, d_nrm, npx * 12, cudaMemcpyDeviceToHost, s);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
         if (e != cudaSuccess) { c->err = std::string("render (host buffers): ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
+        const int rw = wavefront_wait(c);
+        if (rc == PB_OK) rc = rw;
     }
-    cudaFree(d_sum); cudaFree(d_alb); cudaFree(d_nrm);
     return rc;
 }
 
@@ -121,8 +126,17 @@ PB_API int pb_resolve(pb_ctx* c, const float* sum, float* frame, uint32_t n, int
     return rc;
 }
 
+PB_API int pb_wait(pb_ctx* c) {
+    if (!c) return PB_ERR_INVALID;
+    cudaSetDevice(c->device);
+    return wavefront_wait(c);
+}
+
 PB_API int pb_get_stats(pb_ctx* c, pb_stats* out) {
     if (!c || !out) return PB_ERR_INVALID;
+    cudaSetDevice(c->device);
+    int rc = wavefront_wait(c);
+    if (rc != PB_OK) return rc;
     *out = c->stats;
     return PB_OK;
 }

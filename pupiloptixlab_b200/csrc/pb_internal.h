@@ -42,6 +42,8 @@ struct pb_ctx {
 
     // ---- device scene
     float* d_pos = nullptr; float* d_nrm = nullptr; float* d_uv = nullptr; uint32_t* d_idx = nullptr;
+    float* d_stage = nullptr;            // film staging of the host-buffer pb_render path (sum 16 B + albedo 12 B + normal 12 B per pixel), grow-only
+    size_t stage_px = 0;
     float* d_trishade = nullptr;         // 24 floats per triangle (pb_scene.cuh)
     pb::ObjRec* d_objs = nullptr;
     pb::MatRec* d_mats = nullptr;
@@ -94,5 +96,6 @@ int trace_rays(pb_ctx* c, const pb_ray* d_rays, uint64_t n, pb_hit* d_hits, uint
 // pb_wavefront.cu
 int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, cudaStream_t s);
 void wavefront_free(pb_ctx* c);
+int wavefront_wait(pb_ctx* c);   // synchronises pending (PB_RENDER_ASYNC) renders and folds them into pb_stats
 int resolve_frame(pb_ctx* c, const float* d_sum, float* d_frame, uint32_t n, cudaStream_t s);
 }  // namespace pb

@@ -79,6 +79,15 @@ struct Wavefront {
     WfState st{};
     uint32_t cap = 0;
     void* block = nullptr;
+    std::vector<cudaEvent_t> events;   // event pool reused by every call
+    // renders enqueued (PB_RENDER_ASYNC) or running and not yet folded into pb_stats by wavefront_wait()
+    struct Pending {
+        std::vector<cudaEvent_t> whole, ext, con, shd;   // begin / end pairs
+        size_t ev_used = 0;
+        uint32_t launches = 0, calls = 0;
+        uint64_t samples = 0;
+        cudaStream_t stream = nullptr;
+    } pend;
 };
 
 struct WfScene {
@@ -416,17 +425,52 @@ static uint32_t wave_path_target() {
     return (uint32_t)paths;
 }
 
+// Folds every pending render into pb_stats: one stream synchronise, ray / visit totals, summed stage times.
+int wavefront_wait(pb_ctx* c) {
+    if (!c->wf || c->wf->pend.calls == 0) return PB_OK;
+    Wavefront::Pending& pd = c->wf->pend;
+    unsigned long long tot[8];
+    cudaError_t e = cudaMemcpyAsync(tot, c->wf->st.totals, 64, cudaMemcpyDeviceToHost, pd.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(pd.stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    auto sum_pairs = [](std::vector<cudaEvent_t>& v) {
+        float total = 0.f;
+        for (size_t i = 0; i + 1 < v.size(); i += 2) { float t = 0.f; cudaEventElapsedTime(&t, v[i], v[i + 1]); total += t; }
+        return total;
+    };
+    if (e == cudaSuccess) {
+        c->stats.last_render_ms = sum_pairs(pd.whole);
+        c->stats.rays_closest = tot[0]; c->stats.rays_any = tot[1];
+        c->stats.samples = pd.samples;
+        c->stats.kernel_launches = pd.launches;
+        c->stats.node_visits = tot[2]; c->stats.prim_tests_tri = tot[3]; c->stats.prim_tests_sphere = tot[4];
+        c->stats.node_visits_any = tot[5]; c->stats.prim_tests_tri_any = tot[6]; c->stats.prim_tests_sphere_any = tot[7];
+        c->stats.extend_launches = (uint32_t)(pd.ext.size() / 2); c->stats.connect_launches = (uint32_t)(pd.con.size() / 2);
+        c->stats.shade_groups = (uint32_t)(pd.shd.size() / 2);
+        c->stats.extend_ms = sum_pairs(pd.ext); c->stats.connect_ms = sum_pairs(pd.con); c->stats.shade_ms = sum_pairs(pd.shd);
+    }
+    pd.whole.clear(); pd.ext.clear(); pd.con.clear(); pd.shd.clear();
+    pd.ev_used = 0; pd.launches = 0; pd.calls = 0; pd.samples = 0;
+    if (e != cudaSuccess) { c->err = std::string("render: ") + cudaGetErrorString(e); return PB_ERR_CUDA; }
+    return PB_OK;
+}
+
 void wavefront_free(pb_ctx* c) {
     if (!c->wf) return;
+    wavefront_wait(c);
     cudaFree(c->wf->block);
+    for (cudaEvent_t e : c->wf->events) cudaEventDestroy(e);
     delete c->wf;
     c->wf = nullptr;
 }
 
 static int wavefront_reserve(pb_ctx* c, uint32_t cap) {
     if (c->wf && c->wf->cap >= cap) return PB_OK;
+    std::vector<cudaEvent_t> keep;
+    if (c->wf) { wavefront_wait(c); keep.swap(c->wf->events); }
     wavefront_free(c);
     c->wf = new Wavefront();
+    c->wf->events.swap(keep);
     auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
     const size_t n = cap;
     size_t off = 0;
@@ -470,17 +514,23 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     sc.width = p->width; sc.height = p->height; sc.n_px = n_px; sc.max_depth = p->max_depth;
     sc.first_sample = p->first_sample; sc.stride = p->sample_stride ? p->sample_stride : 1u;
 
-    cudaEvent_t e0, e1;
-    PB_CUDA_TRY(c, cudaEventCreate(&e0)); PB_CUDA_TRY(c, cudaEventCreate(&e1));
-    PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 64, s));
+    Wavefront::Pending& pd = c->wf->pend;
+    if (pd.calls && pd.stream != s) { rc = wavefront_wait(c); if (rc != PB_OK) return rc; }   // one stream at a time
+    if (pd.calls == 0) PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 64, s));                   // totals add up over pending calls
+    pd.stream = s;
     const bool counted = (p->flags & PB_RENDER_COUNTED) != 0u, timing = (p->flags & PB_RENDER_STAGE_TIMING) != 0u;
-    std::vector<cudaEvent_t> ev_ext, ev_con, ev_shd;   // begin/end pairs around every traversal launch
-    auto mark = [&](std::vector<cudaEvent_t>& v) {
-        if (!timing) return;
-        cudaEvent_t e;
-        if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, s); v.push_back(e); }
+    auto take_event = [&]() -> cudaEvent_t {
+        std::vector<cudaEvent_t>& pool = c->wf->events;
+        if (pd.ev_used == pool.size()) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) return nullptr; pool.push_back(e); }
+        return pool[pd.ev_used++];
     };
-    cudaEventRecord(e0, s);
+    auto record = [&](std::vector<cudaEvent_t>& v) {
+        cudaEvent_t e = take_event();
+        if (e) { cudaEventRecord(e, s); v.push_back(e); }
+    };
+    auto mark = [&](std::vector<cudaEvent_t>& v) { if (timing) record(v); };
+    std::vector<cudaEvent_t>&ev_ext = pd.ext, &ev_con = pd.con, &ev_shd = pd.shd;
+    record(pd.whole);
     const unsigned g_trace = (unsigned)c->sm_count * 8u, g_shade = (unsigned)c->sm_count * 8u;
     uint32_t launches = 0;
     for (uint32_t k0 = 0; k0 < p->sample_count; k0 += K) {
@@ -518,30 +568,11 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
         k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), n_px, kw);
         ++launches;
     }
-    cudaEventRecord(e1, s);
-    unsigned long long tot[8];
-    PB_CUDA_TRY(c, cudaMemcpyAsync(tot, st.totals, 64, cudaMemcpyDeviceToHost, s));
-    PB_CUDA_TRY(c, cudaStreamSynchronize(s));
+    record(pd.whole);
+    pd.launches += launches; pd.calls += 1; pd.samples += (uint64_t)n_px * p->sample_count;
     PB_CUDA_TRY(c, cudaGetLastError());
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
-    c->stats.last_render_ms = ms;
-    c->stats.rays_closest = tot[0]; c->stats.rays_any = tot[1];
-    c->stats.samples = (uint64_t)n_px * p->sample_count;
-    c->stats.kernel_launches = launches;
-    c->stats.node_visits = tot[2]; c->stats.prim_tests_tri = tot[3]; c->stats.prim_tests_sphere = tot[4];
-    c->stats.node_visits_any = tot[5]; c->stats.prim_tests_tri_any = tot[6]; c->stats.prim_tests_sphere_any = tot[7];
-    auto sum_pairs = [](std::vector<cudaEvent_t>& v) {
-        float total = 0.f;
-        for (size_t i = 0; i + 1 < v.size(); i += 2) { float t = 0.f; cudaEventElapsedTime(&t, v[i], v[i + 1]); total += t; }
-        for (cudaEvent_t e : v) cudaEventDestroy(e);
-        return total;
-    };
-    c->stats.extend_launches = (uint32_t)(ev_ext.size() / 2); c->stats.connect_launches = (uint32_t)(ev_con.size() / 2);
-    c->stats.shade_groups = (uint32_t)(ev_shd.size() / 2);
-    c->stats.extend_ms = sum_pairs(ev_ext); c->stats.connect_ms = sum_pairs(ev_con); c->stats.shade_ms = sum_pairs(ev_shd);
-    return PB_OK;
+    if (p->flags & PB_RENDER_ASYNC) return PB_OK;     // folded into pb_stats by the next pb_wait / pb_get_stats
+    return wavefront_wait(c);
 }
 
 int resolve_frame(pb_ctx* c, const float* d_sum, float* d_frame, uint32_t n, cudaStream_t s) {

@@ -136,3 +136,29 @@ def test_converged_images_match_reference_header_golden(api):
         blk = float(np.max(np.abs(ba - bb) / (bb + 1e-3)))
         print(f"{variant} {spp} spp: rmse(tonemapped) {rmse_tm:.2e}, rel rmse {rel_rmse:.2e}, worst block {blk:.2e}")
         assert rmse_tm <= 1e-3 and rel_rmse <= 2e-3 and blk <= 2e-3, (variant, rmse_tm, rel_rmse, blk)
+
+
+def test_async_renders_fold_into_one_wait(api):
+    """PB_RENDER_ASYNC: two renders enqueued back to back on one stream, one pb_wait — same film as the
+    synchronous calls, stats are the totals of both."""
+    import torch
+    g = capi.Context(api)
+    w = h = 128
+    scenes.cornell_box(g, w, h, "materials")
+    ref, _, _ = g.render(w, h, 6, 0, 4)
+    rays_sync = 0
+    for first in (0, 2):
+        g.render(w, h, 6, first, 2)
+        rays_sync += g.stats()["rays_closest"]
+    d = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        for first, flags in ((0, capi.RENDER_CLEAR | capi.RENDER_ASYNC), (2, capi.RENDER_ASYNC)):
+            g.render_dev(capi.RenderParams(w, h, 6, first, 2, 1, flags, 0), d.data_ptr(), 0, 0, stream.cuda_stream)
+        g.wait()
+        st = g.stats()
+        out = d.cpu().numpy()
+    assert np.array_equal(out.view(np.uint32), ref.view(np.uint32))
+    assert st["rays_closest"] == rays_sync and st["samples"] == 4 * w * h
+    with pytest.raises(capi.ApiError):      # host buffers cannot be asynchronous
+        g.render_into(capi.RenderParams(w, h, 6, 0, 1, 1, capi.RENDER_HOST_BUFFERS | capi.RENDER_ASYNC, 0), ref.copy())
