@@ -91,6 +91,51 @@ def checker_texture(c_patch1, c_patch2, su=1.0, sv=1.0) -> Texture:
     return t
 
 
+_KEEPALIVE: list = []
+ADDRESS_WRAP, ADDRESS_CLAMP, ADDRESS_MIRROR, ADDRESS_BORDER = 0, 1, 2, 3
+FILTER_POINT, FILTER_LINEAR = 0, 1
+
+
+def bitmap_texture(rgba, address_mode=ADDRESS_WRAP, filter_mode=FILTER_LINEAR, su=1.0, sv=1.0) -> Texture:
+    """Bitmap texture from an (h, w, 3|4) float array (util::Texture bitmap, framework/util/texture.h:28-47).
+    The array is kept alive on the returned struct; the library copies the texels when the texture is added."""
+    a = np.asarray(rgba, np.float32)
+    if a.shape[-1] == 3:
+        a = np.concatenate([a, np.ones(a.shape[:2] + (1,), np.float32)], -1)
+    a = np.ascontiguousarray(a, np.float32)
+    t = Texture()
+    t.type = TEX_BITMAP
+    t.uv_r0[:] = (su, 0, 0, 0)
+    t.uv_r1[:] = (0, sv, 0, 0)
+    t.bitmap = a.ctypes.data_as(C.POINTER(C.c_float))
+    t.bitmap_h, t.bitmap_w = a.shape[0], a.shape[1]
+    t.address_mode, t.filter_mode = address_mode, filter_mode
+    _KEEPALIVE.append(a)     # ctypes copies the struct by value into Material / Env: the texels must outlive those copies
+    if len(_KEEPALIVE) > 64:
+        del _KEEPALIVE[0]
+    return t
+
+
+def env_const(r, g, b) -> "Env":
+    e = Env()
+    e.type = ENV_CONSTANT
+    e.radiance[:] = (r, g, b)
+    e.scale = 1.0
+    e.to_world[:] = (1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0)
+    return e
+
+
+def env_map(rgba, scale=1.0, to_world=None) -> "Env":
+    """resource::EnvMap (framework/resource/emitter.h): lat-long radiance bitmap, scale, 3x4 to_world."""
+    e = Env()
+    e.type = ENV_MAP
+    e.scale = scale
+    tw = np.eye(4, dtype=np.float32)[:3] if to_world is None else np.asarray(to_world, np.float32).reshape(-1)[:12].reshape(3, 4)
+    e.to_world[:] = [float(x) for x in tw.reshape(-1)]
+    e.map = bitmap_texture(rgba, ADDRESS_WRAP, FILTER_LINEAR)
+    return e
+
+
 def make_material(mtype, twosided=False, int_ior=1.5046, ext_ior=1.000277, nonlinear=False, reflectance=0.5,
                   specular_reflectance=1.0, specular_transmittance=1.0, alpha=0.1, eta=0.0, k=1.0) -> Material:
     """Defaults follow framework/resource/material.cpp:27-147."""

@@ -45,9 +45,8 @@ static void free_device_scene(pb_ctx* c) {
     cudaFree(c->d_nodes); cudaFree(c->d_prims);
     c->d_pos = c->d_nrm = c->d_uv = nullptr; c->d_idx = nullptr; c->d_objs = nullptr; c->d_mats = nullptr;
     c->d_emit = nullptr; c->d_emit_prefix = nullptr; c->d_env_tables = nullptr; c->d_nodes = nullptr; c->d_prims = nullptr;
-    for (auto t : c->tex_objects) cudaDestroyTextureObject(t);
-    for (auto a : c->tex_arrays) cudaFreeArray(a);
-    c->tex_objects.clear(); c->tex_arrays.clear();
+    for (float* b : c->d_bitmaps) cudaFree(b);
+    c->d_bitmaps.clear();
     c->n_nodes = c->n_prims = 0;
 }
 

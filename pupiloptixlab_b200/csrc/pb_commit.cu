@@ -21,10 +21,13 @@ static int upload(pb_ctx* c, T** dst, const std::vector<T>& src) {
     return PB_OK;
 }
 
-static bool uses_bitmap(const pb_material& m) {
-    return m.reflectance.type == PB_TEX_BITMAP || m.specular_reflectance.type == PB_TEX_BITMAP ||
-           m.specular_transmittance.type == PB_TEX_BITMAP || m.alpha.type == PB_TEX_BITMAP ||
-           m.eta.type == PB_TEX_BITMAP || m.k.type == PB_TEX_BITMAP;
+// device copy of a bitmap texture's texels (CudaTextureManager::GetCudaTexture, cuda/texture.cpp:60-102, keeps a
+// cudaArray + texture object per bitmap; here a plain RGBA float array read by tex_bitmap_sample)
+static const float* device_texels(void* user, const pb_texture& t) {
+    pb_ctx* c = static_cast<pb_ctx*>(user);
+    for (size_t i = 0; i < c->bitmaps.size() && i < c->d_bitmaps.size(); ++i)
+        if (c->bitmaps[i].data() == t.bitmap) return c->d_bitmaps[i];
+    return nullptr;
 }
 
 // World::LoadScene -> RenderObject / EmitterHelper / ComputeProbability, then the device BVH build
@@ -34,12 +37,15 @@ static int commit(pb_ctx* c) {
     c->stats = pb_stats{};
     auto t0 = std::chrono::steady_clock::now();
 
-    // ---- materials
-    std::vector<MatRec> mats;
-    for (auto& m : c->materials) {
-        PB_REQUIRE(!uses_bitmap(m), "bitmap textures are not supported by this build (SURVEY 8f rank 2)");
-        mats.push_back(prep::mat_rec(m));
+    // ---- bitmap texels, then materials
+    for (auto& hb : c->bitmaps) {
+        float* d = nullptr;
+        PB_CUDA_TRY(c, cudaMalloc(&d, hb.size() * sizeof(float)));
+        c->d_bitmaps.push_back(d);
+        PB_CUDA_TRY(c, cudaMemcpy(d, hb.data(), hb.size() * sizeof(float), cudaMemcpyHostToDevice));
     }
+    std::vector<MatRec> mats;
+    for (auto& m : c->materials) mats.push_back(prep::mat_rec(m, device_texels, c));
     // ---- objects + emitters (emitter_index_offset: example/path_tracer/pt_pass.cpp:159-170)
     c->h_objs.clear();
     std::vector<EmitRec> emit;
@@ -58,7 +64,6 @@ static int commit(pb_ctx* c) {
         r.n_prims = o.sphere ? 1u : o.n_tri;
         r.emitter_offset = -1;
         if (o.is_emitter) {
-            PB_REQUIRE(o.area_radiance.type != PB_TEX_BITMAP, "bitmap radiance textures are not supported by this build");
             r.emitter_offset = emitter_offset;
             const float select_weight = prep::emitter_weight(o.area_radiance);
             if (o.sphere) {  // SetSphereAreaEmitter, world/emitter.cpp:224-243
@@ -73,7 +78,7 @@ static int commit(pb_ctx* c) {
                 const float radius = sqrtf(dx * dx + dy * dy + dz * dz);
                 e.p1[0] = radius;
                 e.area = 4 * 3.14159265358979323846f * radius * radius;
-                e.radiance = prep::tex_rec(o.area_radiance);
+                e.radiance = prep::tex_rec(o.area_radiance, device_texels(c, o.area_radiance));
                 e.weight = select_weight * e.area;
                 emit.push_back(e);
                 emitter_offset += 1;
@@ -98,7 +103,7 @@ static int commit(pb_ctx* c) {
                     const float bx = e.p2[0] - e.p0[0], by = e.p2[1] - e.p0[1], bz = e.p2[2] - e.p0[2];
                     const float cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
                     e.area = sqrtf(cx * cx + cy * cy + cz * cz) * 0.5f;
-                    e.radiance = prep::tex_rec(o.area_radiance);
+                    e.radiance = prep::tex_rec(o.area_radiance, device_texels(c, o.area_radiance));
                     e.weight = select_weight * e.area;
                     emit.push_back(e);
                 }
@@ -131,9 +136,50 @@ static int commit(pb_ctx* c) {
         env.p1[0] = ctr.x; env.p1[1] = ctr.y; env.p1[2] = ctr.z;
         env.weight = 1.f;
         c->has_env = true;
-    } else if (c->env.type == PB_ENV_MAP) {
-        c->err = "envmap emitters are not supported by this build (SURVEY 8f rank 2)";
-        return PB_ERR_INVALID;
+    } else if (c->env.type == PB_ENV_MAP) {   // AddEmitter EnvMap + BuildEnvMapCdfTable, world/emitter.cpp:107-149,293-313
+        const pb_texture& mt = c->env.map;
+        PB_REQUIRE(mt.type == PB_TEX_BITMAP && mt.bitmap && mt.bitmap_w >= 2 && mt.bitmap_h >= 2, "environment map needs a bitmap of at least 2 x 2 texels");
+        env.type = EM_ENV_MAP;
+        env.radiance = prep::tex_rec(mt, device_texels(c, mt));
+        env.scale = c->env.scale;
+        V3 ctr = (c->scene_hi + c->scene_lo) * 0.5f;
+        env.p1[0] = ctr.x; env.p1[1] = ctr.y; env.p1[2] = ctr.z;
+        env.weight = 1.f;
+        const float* tw = c->env.to_world;
+        float inv[12];
+        invert_affine(tw, inv);
+        for (int r = 0; r < 3; ++r)
+            for (int k = 0; k < 3; ++k) { env.to_world[3 * r + k] = tw[4 * r + k]; env.to_local[3 * r + k] = inv[4 * r + k]; }
+        const size_t w = mt.bitmap_w, h = mt.bitmap_h;
+        std::vector<float> tab((h + 1) + (w + 1) * h + h, 0.f);   // row_cdf | col_cdf | row_weight
+        float* row_cdf = tab.data();
+        float* col_cdf = row_cdf + (h + 1);
+        float* row_weight = col_cdf + (w + 1) * h;
+        size_t ci = 0, ri = 0;
+        float row_sum = 0.f;
+        row_cdf[ri++] = 0.f;
+        for (size_t y = 0; y < h; ++y) {
+            float col_sum = 0.f;
+            col_cdf[ci++] = 0.f;
+            for (size_t x = 0; x < w; ++x) {
+                const float* px = mt.bitmap + 4 * (y * w + x);
+                col_sum += prep::luminance(px);
+                col_cdf[ci++] = col_sum;
+            }
+            for (size_t x = 1; x < w; ++x) col_cdf[ci - x - 1] /= col_sum;
+            col_cdf[ci - 1] = 1.f;
+            const float weight = std::sin((y + 0.5f) * 3.14159265358979323846f / h);
+            row_weight[y] = weight;
+            row_sum += col_sum * weight;
+            row_cdf[ri++] = row_sum;
+        }
+        for (size_t y = 1; y < h; ++y) row_cdf[ri - y - 1] /= row_sum;
+        row_cdf[ri - 1] = 1.f;
+        env.normalization = 1.f / (row_sum * (2.f * 3.14159265358979323846f / w) * (3.14159265358979323846f / h));
+        env.map_w = (uint32_t)w; env.map_h = (uint32_t)h; env.n_row_cdf = (uint32_t)(h + 1);
+        if (upload(c, &c->d_env_tables, tab)) return PB_ERR_CUDA;
+        env.row_cdf = c->d_env_tables; env.col_cdf = c->d_env_tables + (h + 1); env.row_weight = c->d_env_tables + (h + 1) + (w + 1) * h;
+        c->has_env = true;
     }
     // ComputeProbability, world/emitter.cpp:321-337
     float area_weight_sum = 0.f;

@@ -52,16 +52,26 @@ inline float emitter_weight(const pb_texture& t) {  // GetWeight, world/emitter.
     return w;
 }
 
-inline TexRec tex_rec(const pb_texture& t) {
+// `texels` = device copy of t.bitmap (bitmap textures only; see TexBitmapView)
+inline TexRec tex_rec(const pb_texture& t, const float* texels = nullptr) {
     TexRec r{};
     r.type = t.type;
     for (int k = 0; k < 3; ++k) { r.a[k] = t.a[k]; r.b[k] = t.b[k]; }
     for (int k = 0; k < 4; ++k) { r.r0[k] = t.uv_r0[k]; r.r1[k] = t.uv_r1[k]; }
     r.bitmap_w = t.bitmap_w;
+    if (t.type == PB_TEX_BITMAP) {
+        const unsigned long long p = (unsigned long long)(uintptr_t)texels;
+        r.a[0] = u2f(t.address_mode); r.a[1] = u2f(t.filter_mode); r.a[2] = u2f(texels ? t.bitmap_h : 0u);
+        r.b[0] = u2f((uint32_t)p); r.b[1] = u2f((uint32_t)(p >> 32)); r.b[2] = 0.f;
+    }
     return r;
 }
 
-inline MatRec mat_rec(const pb_material& m) {
+// maps the host texels of a pb_texture to their device copy
+typedef const float* (*texel_lookup)(void* user, const pb_texture& t);
+
+inline MatRec mat_rec(const pb_material& m, texel_lookup dev = nullptr, void* user = nullptr) {
+    auto tex_rec = [&](const pb_texture& t) { return prep::tex_rec(t, dev && t.type == PB_TEX_BITMAP ? dev(user, t) : nullptr); };
     MatRec r{};
     r.type = m.type;
     r.twosided = m.twosided;

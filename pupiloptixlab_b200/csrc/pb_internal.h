@@ -53,8 +53,7 @@ struct pb_ctx {
     uint32_t n_area_emitters = 0;
     bool has_env = false;
     std::vector<pb::ObjRec> h_objs;
-    std::vector<cudaTextureObject_t> tex_objects;
-    std::vector<cudaArray_t> tex_arrays;
+    std::vector<float*> d_bitmaps;       // device copies of `bitmaps` (same order), RGBA float, sampled in software (pb_shade.cuh)
 
     // ---- BVH
     pb::Node8* d_nodes = nullptr;

@@ -140,10 +140,39 @@ PB_HD V3 ggx_sample(V3 wo, float alpha, float xi_x, float xi_y) {  // :39
 }
 
 // ---- textures: framework/cuda/texture.h:33-57 --------------------------------------------------------
+// tex2D<float4> on a normalised-coordinate texture (texture.h:52-54; sampler state cuda/texture.cpp:60-96:
+// wrap / clamp / mirror / border addressing, point or linear filter) done in software on a plain RGBA float
+// array: fp32 bilinear weights instead of the texture unit's 8-bit fixed-point ones, the same function the
+// oracle uses (oracle.cpp sample_bitmap), so both sides agree to rounding.
+PB_HD float tex_addr(uint32_t mode, float x, uint32_t n) {
+    if (mode == 0u) { x = x - floorf(x); return x * (float)n; }
+    if (mode == 2u) { const float f = floorf(x); float fr = x - f; if (((int)f) & 1) fr = 1.f - fr; return fr * (float)n; }
+    return fminf(fmaxf(x, 0.f), 1.f) * (float)n;
+}
+PB_HD V3 tex_texel(const TexBitmapView& b, int x, int y) {
+    const int w = (int)b.w, h = (int)b.h;
+    if (b.address_mode == 0u) { x %= w; if (x < 0) x += w; y %= h; if (y < 0) y += h; }
+    else { x = x < 0 ? 0 : (x >= w ? w - 1 : x); y = y < 0 ? 0 : (y >= h ? h - 1 : y); }
+    const float* p = b.texels + 4 * ((size_t)y * b.w + (size_t)x);
+    return {p[0], p[1], p[2]};
+}
+PB_HD V3 tex_bitmap_sample(const TexRec& t, float u, float v) {
+    const TexBitmapView b = tex_bitmap(t);
+    if (!b.texels || b.w == 0u || b.h == 0u) return v3(0.f);
+    const float x = tex_addr(b.address_mode, u, b.w), y = tex_addr(b.address_mode, v, b.h);
+    if (b.filter_mode == 0u) return tex_texel(b, (int)floorf(x), (int)floorf(y));
+    const float xb = x - 0.5f, yb = y - 0.5f;
+    const int i = (int)floorf(xb), j = (int)floorf(yb);
+    const float fa = xb - (float)i, fb = yb - (float)j;
+    return (1.f - fa) * (1.f - fb) * tex_texel(b, i, j) + fa * (1.f - fb) * tex_texel(b, i + 1, j) +
+           (1.f - fa) * fb * tex_texel(b, i, j + 1) + fa * fb * tex_texel(b, i + 1, j + 1);
+}
+
 PB_HD V3 tex_sample(const TexRec& t, V2 uv) {
     if (t.type == 0u) return {t.a[0], t.a[1], t.a[2]};
     float tx = t.r0[0] * uv.x + t.r0[1] * uv.y + t.r0[2] * 0.f + t.r0[3] * 1.f;
     float ty = t.r1[0] * uv.x + t.r1[1] * uv.y + t.r1[2] * 0.f + t.r1[3] * 1.f;
+    if (t.type == 1u) return tex_bitmap_sample(t, tx, ty);
     tx = tx - (tx > 0.f ? floorf(tx) : ceilf(tx));
     ty = ty - (ty > 0.f ? floorf(ty) : ceilf(ty));
     if (tx < 0.f) tx += 1.f;

@@ -108,13 +108,20 @@ enum { PRIM_TRI = 0u, PRIM_SPHERE = 1u };
 // ---- textures / materials / objects / emitters --------------------------------------------------
 struct TexRec {          // 64 B; mirror of cuda::Texture (framework/cuda/texture.h:9-31)
     uint32_t type;       // 0 rgb, 1 bitmap, 2 checkerboard
-    float a[3];
-    float b[3];
-    uint32_t bitmap_w;   // bitmap: size; data handle below
+    float a[3];          // rgb | patch1 | bitmap: bits of (address mode, filter mode, height)
+    float b[3];          // patch2 | bitmap: b[0..1] = the 64 bits of the device pointer to the RGBA float texels
+    uint32_t bitmap_w;   // bitmap: width
     float r0[4];
     float r1[4];
 };
-struct TexBitmap { unsigned long long tex_obj; };
+// bitmap view of a TexRec (the reference keeps a cudaTextureObject_t in the same union, texture.h:12-19)
+struct TexBitmapView { const float* texels; uint32_t w, h, address_mode, filter_mode; };
+PB_HD TexBitmapView tex_bitmap(const TexRec& t) {
+    TexBitmapView v;
+    v.texels = reinterpret_cast<const float*>((unsigned long long)f2u(t.b[0]) | ((unsigned long long)f2u(t.b[1]) << 32));
+    v.w = t.bitmap_w; v.h = f2u(t.a[2]); v.address_mode = f2u(t.a[0]); v.filter_mode = f2u(t.a[1]);
+    return v;
+}
 
 enum { TEX_REFLECTANCE = 0, TEX_SPEC_REFL, TEX_SPEC_TRANS, TEX_ALPHA, TEX_ETA, TEX_K, TEX_COUNT };
 
@@ -128,7 +135,6 @@ struct alignas(16) MatRec {
     uint32_t nonlinear;
     uint32_t _pad;
     TexRec tex[TEX_COUNT];
-    unsigned long long bitmap[TEX_COUNT];  // cudaTextureObject_t per texture slot (0 if not a bitmap)
 };
 
 enum { OBJ_SPHERE = 1u, OBJ_FLIP_NORMALS = 2u, OBJ_FLIP_TEX = 4u, OBJ_HAS_NORMALS = 8u, OBJ_HAS_UV = 16u };
@@ -151,7 +157,6 @@ struct alignas(16) EmitRec {
     uint32_t type;
     float weight, select_probability, area;
     TexRec radiance;
-    unsigned long long radiance_bitmap;
     float p0[3], p1[3], p2[3];   // tri: world positions | sphere: p0 = centre, p1[0] = radius | env: p0 = colour, p1 = centre
     float n0[3], n1[3], n2[3];
     float t0[2], t1[2], t2[2];

@@ -177,11 +177,31 @@ def cornell_box(ctx: capi.Context, width=256, height=256, variant="diffuse") -> 
                                              eta=(0.200438, 0.924033, 1.10221), k=(3.91295, 2.45285, 2.14219)))
         mats["Floor"] = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True,
                                            reflectance=capi.checker_texture((0.725, 0.71, 0.68), (0.3, 0.3, 0.32), 8, 8)))
+    textured = variant in ("textured", "envmap")
+    if textured:
+        # bitmap textures in every role the reference samples them (cuda/texture.h:52-54): reflectance with linear /
+        # wrap and point / mirror sampling, a roughness map, a bitmap-radiance area light (emitter.cpp:85-100)
+        mats["BackWall"] = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True,
+                                              reflectance=capi.bitmap_texture(procedural_bitmap(48, 32, 1), capi.ADDRESS_WRAP, capi.FILTER_LINEAR, 2, 2)))
+        mats["Floor"] = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True,
+                                           reflectance=capi.bitmap_texture(procedural_bitmap(16, 16, 2), capi.ADDRESS_MIRROR, capi.FILTER_POINT, 3, 3)))
+        mats["TallBox"] = ctx.add_material(M(capi.MAT_ROUGH_CONDUCTOR, specular_reflectance=0.8, eta=(0.200438, 0.924033, 1.10221),
+                                             k=(3.91295, 2.45285, 2.14219),
+                                             alpha=capi.bitmap_texture(0.05 + 0.5 * procedural_bitmap(8, 8, 3), capi.ADDRESS_CLAMP, capi.FILTER_LINEAR)))
+        mats["ShortBox"] = ctx.add_material(M(capi.MAT_ROUGH_PLASTIC, int_ior=1.5, ext_ior=1.0, alpha=0.2,
+                                              reflectance=capi.bitmap_texture(procedural_bitmap(32, 32, 4), capi.ADDRESS_WRAP, capi.FILTER_LINEAR)))
     objs = {}
     for name, (kind, m) in CORNELL.items():
+        if variant == "envmap" and name in ("Ceiling", "Light"):
+            continue      # open top: the box is lit by the environment map only
         ar = capi.rgb_texture(17, 12, 4) if name == "Light" else None
+        if textured and name == "Light":
+            ar = capi.bitmap_texture(procedural_bitmap(8, 8, 5) * np.float32(30.0), capi.ADDRESS_CLAMP, capi.FILTER_LINEAR)
         add = add_rectangle if kind == "rectangle" else add_cube
         objs[name] = add(ctx, m, mats[name], 0, ar)
+    if variant == "envmap":
+        rot = np.array([[0.8, 0, 0.6, 0], [0, 1, 0, 0], [-0.6, 0, 0.8, 0]], np.float32)   # y-rotation: exercises to_world / to_local
+        ctx.set_env(capi.env_map(procedural_envmap(64, 32), scale=1.5, to_world=rot))
     if variant == "materials":
         sph = [
             ((-0.55, 0.25, 0.55), 0.25, M(capi.MAT_DIELECTRIC, int_ior=1.5, ext_ior=1.0)),
@@ -199,6 +219,32 @@ def cornell_box(ctx: capi.Context, width=256, height=256, variant="diffuse") -> 
     set_perspective_camera(ctx, 19.5, width, height, CORNELL_SENSOR)
     ctx.commit()
     return {"width": width, "height": height, "objects": objs, "materials": mats}
+
+
+def procedural_bitmap(w: int, h: int, seed: int) -> np.ndarray:
+    """(h, w, 4) float RGBA test pattern in [0.05, 0.95]: smooth gradients + seeded blocks (no image files)."""
+    rng = np.random.RandomState(seed)
+    y, x = np.mgrid[0:h, 0:w].astype(np.float32)
+    img = np.empty((h, w, 4), np.float32)
+    img[..., 0] = 0.5 + 0.45 * np.sin(2 * np.pi * (x / w + 0.13 * seed))
+    img[..., 1] = 0.5 + 0.45 * np.cos(2 * np.pi * (y / h) * 2 + seed)
+    blocks = rng.uniform(0.05, 0.95, ((h + 3) // 4, (w + 3) // 4)).astype(np.float32)
+    img[..., 2] = np.kron(blocks, np.ones((4, 4), np.float32))[:h, :w]
+    img[..., 3] = 1.0
+    return np.clip(img, 0.05, 0.95).astype(np.float32)
+
+
+def procedural_envmap(w: int, h: int) -> np.ndarray:
+    """(h, w, 4) lat-long sky: blue gradient, warm horizon band and a bright 'sun' patch (so that the row / column
+    CDFs of BuildEnvMapCdfTable, world/emitter.cpp:107-149, are far from uniform)."""
+    y, x = np.mgrid[0:h, 0:w].astype(np.float32)
+    theta = (y + 0.5) / h
+    sky = np.stack([0.25 + 0.3 * theta, 0.35 + 0.35 * theta, 0.9 - 0.3 * theta], -1)
+    sky[np.abs(theta - 0.5) < 0.06] += np.array([0.6, 0.35, 0.1], np.float32)
+    sun = ((x - 0.3 * w) ** 2 / (0.04 * w) ** 2 + (y - 0.22 * h) ** 2 / (0.07 * h) ** 2) < 1.0
+    sky[sun] = (40.0, 36.0, 28.0)
+    sky[theta > 0.55] *= 0.15         # dark ground half
+    return np.concatenate([sky, np.ones((h, w, 1))], -1).astype(np.float32)
 
 
 # ------------------------------------------------------------------------------------------------

@@ -67,7 +67,8 @@ def emitter_inputs(n, seed):
     return hp.astype(np.float32), hn.astype(np.float32), xi.astype(np.float32)
 
 
-RENDERS = [("diffuse", 64, 64, 8, 4), ("materials", 48, 48, 8, 4), ("materials", 40, 24, 2, 2)]
+RENDERS = [("diffuse", 64, 64, 8, 4), ("materials", 48, 48, 8, 4), ("materials", 40, 24, 2, 2),
+           ("textured", 48, 48, 6, 4), ("envmap", 48, 48, 6, 4)]   # bitmap textures / environment map
 
 
 def generate(ctx_factory, n_bsdf=1500, n_emit=600):

@@ -38,7 +38,8 @@ def render_pair(api, oracle_api, variant, w, h, depth, spp, first=0, stride=1):
 
 @pytest.mark.parametrize("variant,w,h,depth,spp", [("diffuse", 256, 256, 8, 1), ("diffuse", 256, 256, 8, 16),
                                                    ("materials", 192, 192, 8, 1), ("materials", 192, 192, 8, 16),
-                                                   ("materials", 64, 48, 1, 2), ("materials", 64, 48, 2, 2)])
+                                                   ("materials", 64, 48, 1, 2), ("materials", 64, 48, 2, 2),
+                                                   ("textured", 160, 160, 8, 4), ("envmap", 160, 160, 8, 4)])
 def test_cornell_matches_oracle(api, oracle_api, variant, w, h, depth, spp):
     o, g, (so, ao, no), (sg, ag, ng) = render_pair(api, oracle_api, variant, w, h, depth, spp)
     assert np.array_equal(sg[..., 3], so[..., 3]) and (sg[..., 3] == spp).all()
@@ -162,3 +163,24 @@ def test_async_renders_fold_into_one_wait(api):
     assert st["rays_closest"] == rays_sync and st["samples"] == 4 * w * h
     with pytest.raises(capi.ApiError):      # host buffers cannot be asynchronous
         g.render_into(capi.RenderParams(w, h, 6, 0, 1, 1, capi.RENDER_HOST_BUFFERS | capi.RENDER_ASYNC, 0), ref.copy())
+
+
+def test_update_instance_rebuilds(api, oracle_api):
+    """pb_update_instance (IAS::Update semantics, world/ias_manager.cpp:116-151): moving one object changes the
+    hits exactly as the oracle's rebuilt scene does."""
+    from tests import util_scenes as U
+    w = h = 96
+    res = {}
+    for name, ctx in (("g", capi.Context(api)), ("o", pyoracle.OracleContext(oracle_api))):
+        info = scenes.cornell_box(ctx, w, h, "materials")
+        obj = info["objects"]["sphere1"]
+        m = np.eye(4, dtype=np.float32)
+        m[:3, :3] *= 0.3
+        m[:3, 3] = (-0.2, 0.9, 0.1)
+        ctx.update_instance(obj, m[:3])
+        rays = U.random_rays(50000, 77)
+        rays["ox"], rays["oy"], rays["oz"] = 0.0, 1.0, 3.0
+        res[name] = (ctx.trace_closest(rays), ctx.render(w, h, 4, 0, 2)[0])
+    assert np.array_equal(res["g"][0]["prim"], res["o"][0]["prim"])
+    assert np.array_equal(res["g"][0]["t"].view(np.uint32), res["o"][0]["t"].view(np.uint32))
+    assert rel_ok_fraction(res["g"][1][..., :3], res["o"][1][..., :3]) >= PIXEL_FRACTION
