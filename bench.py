@@ -297,7 +297,7 @@ def product_main(args):
     rays_c, rays_a, launches = st["rays_closest"], st["rays_any"], st["kernel_launches"] + (args.steps if rank == 0 else 0)
     ext_ms, con_ms, shd_ms, ext_l, con_l = st["extend_ms"], st["connect_ms"], st["shade_ms"], st["extend_launches"], st["connect_launches"]
     step_ms = [round(st["last_render_ms"] / args.steps, 2)]
-    clk = clocks.window() if clocks else None
+    clk = clocks.stop() if clocks else None   # in-process NVML polling delays the per-step enqueue of the e2e loop (measured: +70 ms spikes): off from here
     t = torch.tensor([ms, float(rays_c), float(rays_a), float(launches)], dtype=torch.float64, device=dev)
     if N > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -331,8 +331,6 @@ def product_main(args):
     w0 = time.perf_counter()
     f0.record(stream)
     e2e_each = []
-    if clocks:
-        clocks.begin()
     for i in range(e2e_steps):
         t_i = time.perf_counter()
         e2e_step(args.warmup + i)
@@ -340,10 +338,7 @@ def product_main(args):
     f1.record(stream)
     barrier()
     e2e_ms = max(f0.elapsed_time(f1), (time.perf_counter() - w0) * 1e3 if N == 1 else 0.0)
-    e2e_clk = None
-    if clocks:
-        clocks.end()
-        e2e_clk = clocks.stop()
+
     if N > 1:
         tt = torch.tensor([e2e_ms], dtype=torch.float64, device=dev); dist.all_reduce(tt, op=dist.ReduceOp.MAX); e2e_ms = float(tt[0])
     e2e_value = float(n_px) * S * e2e_steps * N / (e2e_ms * 1e-3) / 1e6
@@ -404,7 +399,7 @@ def product_main(args):
                            "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"},
                 "mrays_per_s": mrays, "rays_per_sample": (rays_c_all + rays_a_all) / samples,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "ms_each": e2e_each, "clocks": e2e_clk},
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "ms_each": e2e_each},
                 "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
                 "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}
         line.update(extra)

@@ -34,6 +34,7 @@ PB_API int pb_create(pb_ctx** out, int device) {
     if (const char* e = getenv("PB_PRIM_BATCH")) { int v = atoi(e); if (v >= 1 && v <= 32) c->prim_batch = (uint32_t)v; }
     if (const char* e = getenv("PB_LEAF_MAX")) { int v = atoi(e); if (v >= 1 && v <= 3) c->leaf_max = (uint32_t)v; }
     if (const char* e = getenv("PB_BOTTOM_MAX")) { int v = atoi(e); if (v >= 0 && v <= 24) c->bottom_max = (uint32_t)v; }
+    if (getenv("PB_NO_GRAPH")) c->use_graphs = false;
     if (const char* e = getenv("PB_REFILL")) { int v = atoi(e); if (v >= 1 && v <= 32) c->refill = (uint32_t)v; }
     return PB_OK;
 }
@@ -146,6 +147,7 @@ PB_API int pb_set_camera(pb_ctx* c, const float s2c[16], const float c2w[16]) {
     if (!c) return PB_ERR_INVALID;
     memcpy(c->cam.s2c, s2c, 64);
     memcpy(c->cam.c2w, c2w, 64);
+    ++c->scene_epoch;
     return PB_OK;
 }
 

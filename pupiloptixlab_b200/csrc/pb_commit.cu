@@ -33,6 +33,7 @@ static const float* device_texels(void* user, const pb_texture& t) {
 // World::LoadScene -> RenderObject / EmitterHelper / ComputeProbability, then the device BVH build
 static int commit(pb_ctx* c) {
     cudaSetDevice(c->device);
+    wavefront_wait(c);          // asynchronous renders may still read the old scene
     pb_free_device_scene(c);
     c->stats = pb_stats{};
     auto t0 = std::chrono::steady_clock::now();
@@ -199,6 +200,7 @@ static int commit(pb_ctx* c) {
     c->stats.n_objects = (uint32_t)c->h_objs.size(); c->stats.bvh_depth = c->bvh_levels;
     c->stats.build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     c->committed = true;
+    ++c->scene_epoch;
     return PB_OK;
 }
 

@@ -1,4 +1,5 @@
 // pb_entry.cu — ray-cast, render, resolve, stats and BVH-export entry points of the C ABI.
+#include <chrono>
 #include <cstring>
 
 #include "pb_internal.h"
@@ -80,6 +81,7 @@ PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba
         return wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, s);   // synchronises unless PB_RENDER_ASYNC
     }
     PB_REQUIRE(!(p->flags & PB_RENDER_ASYNC), "PB_RENDER_ASYNC needs device buffers");
+    const auto h0 = std::chrono::steady_clock::now();
     // film staging lives in the context (no cudaMalloc / cudaFree - both synchronise the device - per call)
     if (c->stage_px < npx) {
         cudaFree(c->d_stage); c->d_stage = nullptr; c->stage_px = 0;
@@ -98,8 +100,14 @@ PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba
         if (e == cudaSuccess && albedo_rgb) e = cudaMemcpyAsync(albedo_rgb, d_alb, npx * 12, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && normal_rgb) e = cudaMemcpyAsync(normal_rgb, d_nrm, npx * 12, cudaMemcpyDeviceToHost, s);
         if (e != cudaSuccess) { c->err = std::string("render (host buffers): ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
+        const auto h1 = std::chrono::steady_clock::now();
         const int rw = wavefront_wait(c);
         if (rc == PB_OK) rc = rw;
+        if (getenv("PB_DEBUG_TIMING")) {
+            const auto h2 = std::chrono::steady_clock::now();
+            auto us = [](auto a, auto b) { return (long)std::chrono::duration_cast<std::chrono::microseconds>(b - a).count(); };
+            fprintf(stderr, "[pb] render(host buffers): enqueue %ld us, wait %ld us, kernels %.2f ms\n", us(h0, h1), us(h1, h2), c->stats.last_render_ms);
+        }
     }
     return rc;
 }

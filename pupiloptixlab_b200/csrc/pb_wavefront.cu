@@ -27,7 +27,7 @@ constexpr int kWfThreads = 128;
 #ifndef PB_TRACE_MIN_BLOCKS
 #define PB_TRACE_MIN_BLOCKS 8   // 64 registers per thread
 #endif
-enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_COUNT = 16 };
+enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_FRAME0 = 13, C_COUNT = 16 };
 enum : uint32_t { F_DEPTH_MASK = 0xffu, F_DELTA = 0x100u };
 constexpr float kRayTmin = 0.001f, kRayTmax = 1e16f;
 // Queue entries are visited in (increasingly random) queue order, so the first touch of a path record is a
@@ -88,6 +88,16 @@ struct Wavefront {
         uint64_t samples = 0;
         cudaStream_t stream = nullptr;
     } pend;
+    // One wave (generate, max_depth x {prepare, extend, miss, shade x 7, after_shade, connect}, accumulate: ~195
+    // launches at depth 16) captured once as a CUDA graph and replayed with a single cudaGraphLaunch.  The host
+    // cost of a step drops from ~200 driver calls to 3, which is what the synchronous host-buffer path is
+    // exposed to (measured on a shared box: the enqueue of one step took 0.8 ms normally and 15-57 ms in bursts).
+    struct WaveGraph {
+        uint64_t epoch; uint32_t width, height, max_depth, stride, kw, k_aov;
+        float *d_sum, *d_albedo, *d_normal;
+        cudaGraphExec_t exec;
+    };
+    std::vector<WaveGraph> graphs;
 };
 
 struct WfScene {
@@ -97,7 +107,8 @@ struct WfScene {
     EmitterTable em;
     Camera cam;
     uint32_t width, height, n_px, max_depth;
-    uint32_t first_sample, stride;
+    uint32_t stride;      // frame index step; the first frame of a wave is s.cnt[C_FRAME0] (set per wave, so that a
+                          // captured wave graph can be replayed for any first_sample)
 };
 
 // ---- warp-aggregated queue append: every lane of the warp must call ---------------------------------
@@ -121,15 +132,16 @@ __global__ void k_prepare(WfState s, int cur, uint32_t set_cur_count, int set) {
     s.cnt[C_CUR_EXT] = 0; s.cnt[C_CUR_CON] = 0;
 }
 __global__ void k_after_shade(WfState s) { s.totals[1] += s.cnt[C_SHADOW]; }
+__global__ void k_set_frame0(WfState s, uint32_t frame0) { s.cnt[C_FRAME0] = frame0; }
 
 // ---- generate: camera rays of K frames (main.cu:37-75) ----------------------------------------------
-__global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_t wave_first_k, uint32_t n_paths) {
+__global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_t n_paths) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= n_paths) return;
     const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
     const uint32_t x = pixel % sc.width, y = pixel / sc.width;
     Rng rng;
-    rng.init(pixel, sc.first_sample + (wave_first_k + k) * sc.stride);
+    rng.init(pixel, s.cnt[C_FRAME0] + k * sc.stride);
     const float jx = rng.next(), jy = rng.next();
     const float sx = (static_cast<float>(x) + jx) / static_cast<float>(sc.width);
     const float sy = (static_cast<float>(y) + jy) / static_cast<float>(sc.height);
@@ -460,6 +472,7 @@ void wavefront_free(pb_ctx* c) {
     wavefront_wait(c);
     cudaFree(c->wf->block);
     for (cudaEvent_t e : c->wf->events) cudaEventDestroy(e);
+    for (auto& g : c->wf->graphs) cudaGraphExecDestroy(g.exec);
     delete c->wf;
     c->wf = nullptr;
 }
@@ -512,7 +525,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     sc.em = EmitterTable{c->d_emit, c->d_emit_prefix, c->n_area_emitters};
     sc.cam = c->cam;
     sc.width = p->width; sc.height = p->height; sc.n_px = n_px; sc.max_depth = p->max_depth;
-    sc.first_sample = p->first_sample; sc.stride = p->sample_stride ? p->sample_stride : 1u;
+    sc.stride = p->sample_stride ? p->sample_stride : 1u;
 
     Wavefront::Pending& pd = c->wf->pend;
     if (pd.calls && pd.stream != s) { rc = wavefront_wait(c); if (rc != PB_OK) return rc; }   // one stream at a time
@@ -532,41 +545,70 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     std::vector<cudaEvent_t>&ev_ext = pd.ext, &ev_con = pd.con, &ev_shd = pd.shd;
     record(pd.whole);
     const unsigned g_trace = (unsigned)c->sm_count * 8u, g_shade = (unsigned)c->sm_count * 8u;
+    const bool use_graph = c->use_graphs && !counted && !timing;   // event records stay on the plain launch path
+    if (!c->wf->graphs.empty() && c->wf->graphs.front().epoch != c->scene_epoch) {
+        if (pd.calls) { rc = wavefront_wait(c); if (rc != PB_OK) return rc; pd.stream = s; PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 64, s)); }
+        for (auto& g : c->wf->graphs) cudaGraphExecDestroy(g.exec);
+        c->wf->graphs.clear();
+    }
     uint32_t launches = 0;
     for (uint32_t k0 = 0; k0 < p->sample_count; k0 += K) {
         const uint32_t kw = std::min(K, p->sample_count - k0);
         const uint32_t n_paths = kw * n_px;
         const bool last_wave = k0 + kw >= p->sample_count;
         const uint32_t k_aov = last_wave ? kw - 1 : 0xFFFFFFFFu;   // AOVs of the last frame (main.cu:94-99)
-        k_generate<<<(n_paths + 255) / 256, 256, 0, s>>>(st, sc, k0, n_paths);
+        k_set_frame0<<<1, 1, 0, s>>>(st, p->first_sample + k0 * sc.stride);
         ++launches;
-        int cur = 0;
-        for (uint32_t b = 0; b < std::max(1u, p->max_depth); ++b) {
-            k_prepare<<<1, 1, 0, s>>>(st, cur, n_paths, b == 0 ? 1 : 0);
-            mark(ev_ext);
-            if (counted) k_extend<true><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
-            else k_extend<false><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
-            mark(ev_ext);
-            mark(ev_shd);
-            k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, d_albedo, d_normal);
-            launch_shade<1>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-            launch_shade<2>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-            launch_shade<3>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-            launch_shade<4>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-            launch_shade<5>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-            launch_shade<6>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-            launch_shade<7>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-            k_after_shade<<<1, 1, 0, s>>>(st);
-            mark(ev_shd);
-            mark(ev_con);
-            if (counted) k_connect<true><<<g_trace, kWfThreads, 0, s>>>(st, sc);
-            else k_connect<false><<<g_trace, kWfThreads, 0, s>>>(st, sc);
-            mark(ev_con);
-            launches += 12;
-            cur ^= 1;
+        auto enqueue_wave = [&]() {
+            k_generate<<<(n_paths + 255) / 256, 256, 0, s>>>(st, sc, n_paths);
+            int cur = 0;
+            for (uint32_t b = 0; b < std::max(1u, p->max_depth); ++b) {
+                k_prepare<<<1, 1, 0, s>>>(st, cur, n_paths, b == 0 ? 1 : 0);
+                mark(ev_ext);
+                if (counted) k_extend<true><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
+                else k_extend<false><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
+                mark(ev_ext);
+                mark(ev_shd);
+                k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, d_albedo, d_normal);
+                launch_shade<1>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                launch_shade<2>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                launch_shade<3>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                launch_shade<4>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                launch_shade<5>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                launch_shade<6>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                launch_shade<7>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                k_after_shade<<<1, 1, 0, s>>>(st);
+                mark(ev_shd);
+                mark(ev_con);
+                if (counted) k_connect<true><<<g_trace, kWfThreads, 0, s>>>(st, sc);
+                else k_connect<false><<<g_trace, kWfThreads, 0, s>>>(st, sc);
+                mark(ev_con);
+                cur ^= 1;
+            }
+            k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), n_px, kw);
+        };
+        launches += 2u + 12u * std::max(1u, p->max_depth);
+        cudaGraphExec_t exec = nullptr;
+        if (use_graph) {
+            for (auto& g : c->wf->graphs)
+                if (g.epoch == c->scene_epoch && g.width == p->width && g.height == p->height && g.max_depth == p->max_depth &&
+                    g.stride == sc.stride && g.kw == kw && g.k_aov == k_aov && g.d_sum == d_sum && g.d_albedo == d_albedo && g.d_normal == d_normal)
+                    exec = g.exec;
+            if (!exec && cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+                enqueue_wave();
+                cudaGraph_t graph = nullptr;
+                if (cudaStreamEndCapture(s, &graph) == cudaSuccess && graph && cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess) {
+                    if (c->wf->graphs.size() >= 8 && pd.calls == 0) { cudaGraphExecDestroy(c->wf->graphs.front().exec); c->wf->graphs.erase(c->wf->graphs.begin()); }
+                    c->wf->graphs.push_back({c->scene_epoch, p->width, p->height, p->max_depth, sc.stride, kw, k_aov, d_sum, d_albedo, d_normal, exec});
+                } else {
+                    exec = nullptr;
+                }
+                if (graph) cudaGraphDestroy(graph);
+                (void)cudaGetLastError();
+            }
         }
-        k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), n_px, kw);
-        ++launches;
+        if (exec) PB_CUDA_TRY(c, cudaGraphLaunch(exec, s));
+        else enqueue_wave();
     }
     record(pd.whole);
     pd.launches += launches; pd.calls += 1; pd.samples += (uint64_t)n_px * p->sample_count;
