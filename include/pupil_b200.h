@@ -193,6 +193,13 @@ PB_API int pb_render(pb_ctx* ctx, const pb_render_params* p, float* accum_sum_rg
 PB_API int pb_resolve(pb_ctx* ctx, const float* accum_sum_rgba, float* frame_rgba, uint32_t n_pixels,
                       int host, void* cuda_stream);
 
+/* display transform of the reference's output pass (framework/system/gui/output.hlsl:30-73): optional ACES
+ * tone mapping (adapted luminance 1), optional gamma 2.2, then the UNORM8 conversion the swap chain's render
+ * target performs (saturate, x * 255 + 0.5).  frame_rgba = n_pixels float4 (pb_resolve's output), rgba8 =
+ * n_pixels * 4 bytes in the same pixel order (the shader's vertical flip belongs to the window, not the data). */
+PB_API int pb_tonemap(pb_ctx* ctx, const float* frame_rgba, uint8_t* rgba8, uint32_t n_pixels, int tone_mapping,
+                      int gamma_correct, int host, void* cuda_stream);
+
 /* waits for renders enqueued with PB_RENDER_ASYNC (replaces Pass::Synchronize, framework/optix/pass.h:88) */
 PB_API int pb_wait(pb_ctx* ctx);
 /* implies pb_wait */

@@ -196,8 +196,9 @@ class Api:
         f("render", i32, [vp, C.POINTER(RenderParams), vp, vp, vp, vp])
         f("resolve", i32, [vp, vp, vp, u32, i32, vp])
         f("get_stats", i32, [vp, C.POINTER(Stats)])
-        if self.prefix == "pb_":      # the oracle is synchronous
+        if self.prefix == "pb_":      # the oracle is synchronous and has no display transform
             f("wait", i32, [vp])
+            f("tonemap", i32, [vp, vp, vp, u32, i32, i32, i32, vp])
 
     def _f(self, name, res, args, optional=False):
         try:
@@ -327,6 +328,13 @@ class Context:
     def render_into(self, params: RenderParams, acc: np.ndarray):
         """Host-buffer render accumulating into an existing host array."""
         self._ck(self.api._render(self.h, C.byref(params), acc.ctypes.data, None, None, None), "render")
+
+    def tonemap(self, frame_rgba: np.ndarray, tone_mapping=True, gamma_correct=True) -> np.ndarray:
+        """output.hlsl display transform of a resolved float4 frame (host arrays) -> uint8 RGBA."""
+        a = np.ascontiguousarray(frame_rgba, np.float32)
+        out = np.zeros(a.shape[:-1] + (4,), np.uint8)
+        self._ck(self.api._tonemap(self.h, a.ctypes.data, out.ctypes.data, a.size // 4, int(tone_mapping), int(gamma_correct), 1, None), "tonemap")
+        return out
 
     def wait(self):
         """Synchronises renders enqueued with RENDER_ASYNC."""

@@ -134,6 +134,32 @@ PB_API int pb_resolve(pb_ctx* c, const float* sum, float* frame, uint32_t n, int
     return rc;
 }
 
+PB_API int pb_tonemap(pb_ctx* c, const float* frame, uint8_t* rgba8, uint32_t n, int tone, int gamma, int host, void* stream) {
+    if (!c) return PB_ERR_INVALID;
+    PB_REQUIRE(n == 0 || (frame && rgba8), "null frame / output buffer");
+    cudaSetDevice(c->device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    if (!host) {
+        int rc = tonemap_frame(c, frame, rgba8, n, tone, gamma, s);
+        if (rc != PB_OK) return rc;
+        PB_CUDA_TRY(c, cudaStreamSynchronize(s));
+        return PB_OK;
+    }
+    float* d_a = nullptr;
+    uint8_t* d_b = nullptr;
+    PB_CUDA_TRY(c, cudaMalloc(&d_a, (size_t)n * 16 + 16));
+    cudaError_t e = cudaMalloc(&d_b, (size_t)n * 4 + 4);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_a, frame, (size_t)n * 16, cudaMemcpyHostToDevice, s);
+    int rc = e == cudaSuccess ? tonemap_frame(c, d_a, d_b, n, tone, gamma, s) : PB_ERR_CUDA;
+    if (rc == PB_OK) {
+        e = cudaMemcpyAsync(rgba8, d_b, (size_t)n * 4, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    }
+    cudaFree(d_a); cudaFree(d_b);
+    if (e != cudaSuccess) { c->err = std::string("tonemap: ") + cudaGetErrorString(e); return PB_ERR_CUDA; }
+    return rc;
+}
+
 PB_API int pb_wait(pb_ctx* c) {
     if (!c) return PB_ERR_INVALID;
     cudaSetDevice(c->device);

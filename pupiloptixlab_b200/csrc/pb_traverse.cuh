@@ -87,9 +87,6 @@ struct LaneStack {
 // = 0x47000000 + 128 q = the float 32768 + q / 2, so the plane scale is doubled (plane_scale) and the folded
 // bias is 65536 a (error a * 2^-7, still < 1 % of a step).  IDP issues on the FMA-heavy pipe, which the node
 // test leaves idle (ncu v6: ALU 60 % busy, FMA 22 %); 48 PRMT per node were 30 % of the node test's ALU work.
-#ifndef PB_PRIM_PREFETCH
-#define PB_PRIM_PREFETCH 0
-#endif
 #ifndef PB_BYTE_DP4A
 #define PB_BYTE_DP4A 1
 #endif
@@ -202,14 +199,6 @@ struct Traversal {
             G.y = (hits & 0xff000000u) | (n0.w >> 24);
             P.x = n1.y;
             P.y = hits & 0x00ffffffu;
-#if defined(__CUDA_ARCH__) && PB_PRIM_PREFETCH
-            // the lane now waits for the warp's primitive batch: start fetching its first records (L1) meanwhile
-            if (P.y) {
-                const V4* pf = sc.prims + 3ull * (P.x + (uint32_t)lo_bit(P.y));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + 5));
-            }
-#endif
         }
         const bool has_p = alive && P.y != 0u;
 #if defined(__CUDA_ARCH__)

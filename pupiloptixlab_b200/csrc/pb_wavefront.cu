@@ -617,6 +617,30 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     return wavefront_wait(c);
 }
 
+// output.hlsl:30-73 (ACESToneMapping, GammaCorrection, PSMain) + the UNORM8 store of the render target
+__global__ void k_tonemap(const float4* __restrict__ frame, uchar4* __restrict__ out, uint32_t n, int tone, int gamma) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 v = frame[i];
+    float c[3] = {v.x, v.y, v.z};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float x = c[k];
+        if (tone) x = (x * (2.51f * x + 0.03f)) / (x * (2.43f * x + 0.59f) + 0.14f);
+        if (gamma) x = powf(x, 1.f / 2.2f);
+        x = fminf(fmaxf(x, 0.f), 1.f);          // NaN -> 0, as the UNORM conversion does
+        c[k] = floorf(x * 255.f + 0.5f);
+    }
+    out[i] = make_uchar4((unsigned char)c[0], (unsigned char)c[1], (unsigned char)c[2], 255);
+}
+
+int tonemap_frame(pb_ctx* c, const float* d_frame, uint8_t* d_rgba8, uint32_t n, int tone, int gamma, cudaStream_t s) {
+    if (n == 0) return PB_OK;
+    k_tonemap<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float4*>(d_frame), reinterpret_cast<uchar4*>(d_rgba8), n, tone, gamma);
+    PB_CUDA_TRY(c, cudaGetLastError());
+    return PB_OK;
+}
+
 int resolve_frame(pb_ctx* c, const float* d_sum, float* d_frame, uint32_t n, cudaStream_t s) {
     if (n == 0) return PB_OK;
     k_resolve<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float4*>(d_sum), reinterpret_cast<float4*>(d_frame), n);

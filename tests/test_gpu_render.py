@@ -184,3 +184,34 @@ def test_update_instance_rebuilds(api, oracle_api):
     assert np.array_equal(res["g"][0]["prim"], res["o"][0]["prim"])
     assert np.array_equal(res["g"][0]["t"].view(np.uint32), res["o"][0]["t"].view(np.uint32))
     assert rel_ok_fraction(res["g"][1][..., :3], res["o"][1][..., :3]) >= PIXEL_FRACTION
+
+
+def test_tonemap_matches_output_hlsl(api):
+    """pb_tonemap = output.hlsl:30-73 (ACES, gamma 2.2) + UNORM8 store; numpy restatement, <= 1 LSB (powf)."""
+    g = capi.Context(api)
+    rng = np.random.RandomState(4)
+    frame = np.concatenate([rng.gamma(0.7, 1.5, (37, 53, 3)), np.ones((37, 53, 1))], -1).astype(np.float32)
+    frame[0, 0, :3] = (0.0, 1e6, np.nan)
+    for tone in (False, True):
+        for gamma in (False, True):
+            got = g.tonemap(frame, tone, gamma)
+            c = frame[..., :3].astype(np.float32)
+            if tone:
+                c = (c * (np.float32(2.51) * c + np.float32(0.03))) / (c * (np.float32(2.43) * c + np.float32(0.59)) + np.float32(0.14))
+            if gamma:
+                with np.errstate(invalid="ignore"):
+                    c = np.power(c, np.float32(1 / 2.2), dtype=np.float32)
+            c = np.where(np.isnan(c), 0, np.clip(c, 0, 1))
+            want = np.floor(c * 255 + 0.5).astype(np.int32)
+            assert np.abs(got[..., :3].astype(np.int32) - want).max() <= 1
+            assert (got[..., 3] == 255).all()
+    assert (g.tonemap(frame, True, True)[0, 0, :3] == (0, 255, 0)).all()
+
+
+def test_c2_full_size_matches_oracle(api, oracle_api):
+    """C2 at BASELINE.json's film size (1024 x 1024, seven materials + spheres, depth 8); 2 spp so that the oracle
+    finishes in seconds.  Same tolerance as the small cases."""
+    o, g, (so, ao, no), (sg, ag, ng) = render_pair(api, oracle_api, "materials", 1024, 1024, 8, 2)
+    assert np.array_equal(sg[..., 3], so[..., 3])
+    assert rel_ok_fraction(sg[..., :3], so[..., :3]) >= PIXEL_FRACTION
+    assert rel_ok_fraction(ag, ao) >= PIXEL_FRACTION and rel_ok_fraction(ng, no) >= PIXEL_FRACTION
