@@ -67,6 +67,15 @@ PH_API const ph_sink* ph_default_sink(void);
 PH_API int  ph_run_path_tracer(const char* xml_path, int device, uint32_t frames, float* final_rgba,
                                float* albedo_rgb, float* normal_rgb, uint32_t* out_w, uint32_t* out_h);
 
+/* util::BitmapTexture::Load / Save (framework/util/texture.cpp:87-180).  Load: PNG / BMP / TGA / PPM through the
+ * reference's pow(x/255, 2.2) decode, Radiance .hdr / OpenEXR (scanline; none / zips / zip) / PFM as float data;
+ * returns RGBA float texels (row 0 = top) in a buffer released by ph_image_free.  Save: by extension .hdr / .exr
+ * (rows flipped and channel order as the reference writes them) / .pfm.  ph_image_save_png8 writes pb_tonemap's output. */
+PH_API int  ph_image_load(const char* path, float** rgba, uint32_t* w, uint32_t* h);
+PH_API void ph_image_free(float* rgba);
+PH_API int  ph_image_save(const char* path, const float* rgba, uint32_t w, uint32_t h);
+PH_API int  ph_image_save_png8(const char* path, const uint8_t* rgba8, uint32_t w, uint32_t h);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,7 +52,7 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
 
 HOST_DIR = os.path.join(HERE, "host")
 HOST_OUT = os.path.join(HOST_DIR, "libpupil_host.so")
-HOST_SOURCES = ["scene_xml.cpp", "b200_pt_pass.cpp", "host_capi.cpp"]
+HOST_SOURCES = ["scene_xml.cpp", "image_io.cpp", "b200_pt_pass.cpp", "host_capi.cpp"]
 
 
 def build_host(force: bool = False) -> str:
@@ -66,7 +66,7 @@ def build_host(force: bool = False) -> str:
     cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
     cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-function", "-shared",
            "-I", os.path.join(cuda, "include"), *[os.path.join(HOST_DIR, f) for f in HOST_SOURCES], "-o", HOST_OUT,
-           "-L", CSRC, "-lpupil_b200", "-L", os.path.join(cuda, "lib64"), "-lcudart", "-Wl,-rpath,$ORIGIN/../csrc",
+           "-L", CSRC, "-lpupil_b200", "-L", os.path.join(cuda, "lib64"), "-lcudart", "-lz", "-Wl,-rpath,$ORIGIN/../csrc",
            "-Wl,-rpath," + os.path.join(cuda, "lib64")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

@@ -2,6 +2,10 @@
 #include <cstring>
 
 #include "b200_pt_pass.h"
+#include <cstdlib>
+#include <cstring>
+
+#include "image_io.h"
 #include "scene_xml.h"
 
 using namespace pupil::host;
@@ -84,6 +88,29 @@ PH_API int ph_scene_upload(const ph_scene* s, const ph_sink* sink, void* ctx) {
     if (!s || !ctx) return PB_ERR_INVALID;
     g_err.clear();
     return upload_scene(s->scene, sink ? *sink : g_default_sink, ctx, g_err);
+}
+
+PH_API int ph_image_load(const char* path, float** rgba, uint32_t* w, uint32_t* h) {
+    g_err.clear();
+    if (!path || !rgba || !w || !h) { g_err = "null argument"; return PB_ERR_INVALID; }
+    pupil::host::Image img;
+    if (!pupil::host::load_image(path, img, g_err)) return PB_ERR_INVALID;
+    float* p = static_cast<float*>(malloc(img.rgba.size() * sizeof(float)));
+    if (!p) { g_err = "out of memory"; return PB_ERR_INVALID; }
+    memcpy(p, img.rgba.data(), img.rgba.size() * sizeof(float));
+    *rgba = p; *w = (uint32_t)img.w; *h = (uint32_t)img.h;
+    return PB_OK;
+}
+PH_API void ph_image_free(float* rgba) { free(rgba); }
+PH_API int ph_image_save(const char* path, const float* rgba, uint32_t w, uint32_t h) {
+    g_err.clear();
+    if (!path) { g_err = "null path"; return PB_ERR_INVALID; }
+    return pupil::host::save_image(path, rgba, (int)w, (int)h, g_err) ? PB_OK : PB_ERR_INVALID;
+}
+PH_API int ph_image_save_png8(const char* path, const uint8_t* rgba8, uint32_t w, uint32_t h) {
+    g_err.clear();
+    if (!path || !rgba8 || !w || !h) { g_err = "null argument"; return PB_ERR_INVALID; }
+    return pupil::host::save_png8(path, rgba8, (int)w, (int)h, g_err) ? PB_OK : PB_ERR_INVALID;
 }
 
 PH_API int ph_run_path_tracer(const char* xml_path, int device, uint32_t frames, float* final_rgba, float* albedo_rgb,

@@ -6,6 +6,9 @@
 #include <fstream>
 #include <sstream>
 
+#include <map>
+
+#include "image_io.h"
 #include "ior_tables.h"
 
 namespace pupil::host {
@@ -187,6 +190,8 @@ struct Loader {
     Scene& sc;
     std::string& err;
     bool failed = false;
+    struct BitmapRef { const float* texels; uint32_t w, h; };
+    std::map<std::string, BitmapRef> bitmap_cache;
 
     void warn(const std::string& m) { sc.warnings.push_back(m); }
     void fail(const std::string& m) { if (!failed) err = m; failed = true; }
@@ -238,11 +243,30 @@ struct Loader {
             if (parse_float3(o->GetProperty("scale"), v, zero, true)) tr.Scale(v[0], v[1], v[2]);
         } else warn("transform [" + o->var_name + "] UNKNOWN");
     }
+    // TextureManager::GetTexture (resource/texture.cpp): one load per path, texels kept by the scene
+    pb_texture bitmap_texture(const std::string& file) {
+        pb_texture t = color_texture(0.f, 0.f, 0.f);
+        const std::string path = sc.root_path.empty() || (!file.empty() && file[0] == '/') ? file : sc.root_path + "/" + file;
+        auto it = bitmap_cache.find(path);
+        if (it == bitmap_cache.end()) {
+            Image img;
+            std::string e;
+            if (!load_image(path, img, e)) { fail(e); return t; }
+            sc.bitmaps.emplace_back(new std::vector<float>(std::move(img.rgba)));
+            it = bitmap_cache.emplace(path, BitmapRef{sc.bitmaps.back()->data(), (uint32_t)img.w, (uint32_t)img.h}).first;
+        }
+        t.type = PB_TEX_BITMAP;
+        t.bitmap = it->second.texels; t.bitmap_w = it->second.w; t.bitmap_h = it->second.h;
+        return t;
+    }
     // Scene::LoadXmlObj case _texture, scene.cpp:141-180
     pb_texture texture(const XObject* o) {
         pb_texture t = color_texture(0.f, 0.f, 0.f);
-        if (o->type == "bitmap") {
-            fail("bitmap texture '" + o->GetProperty("filename") + "': image loading is not part of this build (SURVEY 8f rank 1)");
+        if (o->type == "bitmap") {                       // scene.cpp:144-165
+            t = bitmap_texture(o->GetProperty("filename"));
+            t.filter_mode = o->GetProperty("filter_type") == "bilinear" ? 1u : 0u;
+            const std::string wrap = o->GetProperty("wrap_mode");
+            t.address_mode = wrap == "mirror" ? 2u : (wrap == "clamp" ? 1u : 0u);   // default is repeat
         } else if (o->type == "checkerboard") {
             const float d0[3] = {0.4f, 0.4f, 0.4f}, d1[3] = {0.2f, 0.2f, 0.2f};
             t.type = PB_TEX_CHECKERBOARD;
@@ -390,8 +414,18 @@ struct Loader {
             sc.env.type = PB_ENV_CONSTANT;
             parse_float3(o->GetProperty("radiance"), sc.env.radiance, zero, true);
             sc.has_env = true;
-        } else if (o->type == "envmap") {
-            fail("envmap emitter '" + o->GetProperty("filename") + "': image loading is not part of this build (SURVEY 8f rank 1-2)");
+        } else if (o->type == "envmap") {                // scene.cpp:208-220
+            sc.env = pb_env{};
+            sc.env.type = PB_ENV_MAP;
+            load_float(o, "scale", sc.env.scale, 1.f);
+            sc.env.map = bitmap_texture(o->GetProperty("filename"));
+            sc.env.map.filter_mode = 1u;                  // Linear
+            sc.env.map.address_mode = 0u;                 // Wrap
+            Transform tr;
+            transform(o->GetUniqueSubObject("transform"), tr);
+            for (int r = 0; r < 3; ++r)
+                for (int k = 0; k < 4; ++k) sc.env.to_world[4 * r + k] = tr.matrix.at(r, k);
+            sc.has_env = true;
         } else if (o->type == "point" || o->type == "area") {
             if (o->type == "point") warn("point emitters are parsed and ignored (as in the reference)");
         } else {

@@ -122,6 +122,35 @@ class Scene:
             raise HostError(f"{self.lib.ph_last_error().decode()}: {ctx.api._last_error(ctx.h).decode()}")
 
 
+def load_image(path: str) -> np.ndarray:
+    """BitmapTexture::Load: (h, w, 4) float32 texels, row 0 = top."""
+    lib = load()
+    p, w, h = C.POINTER(C.c_float)(), _u32(), _u32()
+    lib.ph_image_load.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    lib.ph_image_free.argtypes = [C.POINTER(C.c_float)]
+    if lib.ph_image_load(path.encode(), C.byref(p), C.byref(w), C.byref(h)) != 0:
+        raise HostError(lib.ph_last_error().decode())
+    out = np.ctypeslib.as_array(p, shape=(h.value, w.value, 4)).copy()
+    lib.ph_image_free(p)
+    return out
+
+
+def save_image(path: str, rgba: np.ndarray):
+    """BitmapTexture::Save by extension (.hdr / .exr as the reference writes them, .pfm); uint8 input -> 8-bit PNG."""
+    lib = load()
+    a = np.ascontiguousarray(rgba)
+    h, w = a.shape[:2]
+    if a.dtype == np.uint8:
+        lib.ph_image_save_png8.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        rc = lib.ph_image_save_png8(path.encode(), a.ctypes.data, w, h)
+    else:
+        a = np.ascontiguousarray(a, np.float32)
+        lib.ph_image_save.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        rc = lib.ph_image_save(path.encode(), a.ctypes.data, w, h)
+    if rc != 0:
+        raise HostError(lib.ph_last_error().decode())
+
+
 def run_path_tracer(xml_path: str, frames: int, device: int = 0, width: int | None = None, height: int | None = None):
     """Headless System + B200PTPass: returns (final_rgba[h,w,4] running mean, albedo[h,w,3], normal[h,w,3])."""
     lib = load()
