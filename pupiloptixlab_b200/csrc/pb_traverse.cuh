@@ -90,6 +90,12 @@ struct LaneStack {
 #ifndef PB_BYTE_DP4A
 #define PB_BYTE_DP4A 1
 #endif
+// byte J of w, zero-extended: one PRMT (the compiler's shift + mask are two ALU instructions)
+#if defined(__CUDA_ARCH__)
+template<int J> PB_D uint32_t byte_u(uint32_t w) { return __byte_perm(w, 0u, 0x4440u | J); }
+#else
+template<int J> inline uint32_t byte_u(uint32_t w) { return (w >> (8 * J)) & 0xffu; }
+#endif
 #if defined(__CUDA_ARCH__) && PB_BYTE_DP4A
 template<int J> PB_D float byte_f(uint32_t w, uint32_t k47) { return __uint_as_float(__dp4a(w, 128u << (8 * J), k47)); }
 PB_D float plane_scale(float s) { return __fmul_rn(s, 2.0f); }
@@ -144,7 +150,7 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
             const float tnz = f_fma(byte_f<J>(qnz, k47), az, bnz), tfz = f_fma(byte_f<J>(qfz, k47), az, bfz);   \
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                           \
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                           \
-            const uint32_t bits = ((child_bits4 >> (8 * J)) & 0xffu) << ((bit_index4 >> (8 * J)) & 0xffu);      \
+            const uint32_t bits = byte_u<J>(child_bits4) << ((bit_index4 >> (8 * J)) & 0xffu);                  \
             mask |= tn <= tf ? bits : 0u;                                                                        \
         }
         PB_CHILD(0) PB_CHILD(1) PB_CHILD(2) PB_CHILD(3)
