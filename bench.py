@@ -314,35 +314,47 @@ def product_main(args):
     h_sum = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32).pin_memory()
     h_ptr = h_sum.data_ptr()
 
-    def e2e_step(i):
+    def e2e_step(i, asynchronous):
         # accumulate into the caller's host buffer: upload of the running sums + download of the new ones
-        p = step_params(i, capi.RENDER_HOST_BUFFERS | (capi.RENDER_CLEAR if N > 1 else 0))
+        p = step_params(i, capi.RENDER_HOST_BUFFERS | (capi.RENDER_CLEAR if N > 1 else 0) | (capi.RENDER_ASYNC if asynchronous else 0))
         g.render_dev(p, h_ptr, 0, 0, sp)
         if N > 1:   # per-rank host result -> device -> NCCL reduce -> host on rank 0
             d_sum.copy_(h_sum, non_blocking=True)
             dist.reduce(d_sum, dst=0)
             if rank == 0:
                 h_sum.copy_(d_sum, non_blocking=True)
-        torch.cuda.synchronize(dev)
+        if not asynchronous:
+            torch.cuda.synchronize(dev)
 
+    def e2e_run(asynchronous):
+        e2e_step(0, False)
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.perf_counter()
+        f0.record(stream)
+        each = []
+        for i in range(e2e_steps):
+            t_i = time.perf_counter()
+            e2e_step(args.warmup + i, asynchronous)
+            each.append(round((time.perf_counter() - t_i) * 1e3, 2))
+        if asynchronous:
+            g.wait()
+        f1.record(stream)
+        barrier()
+        t_ms = max(f0.elapsed_time(f1), (time.perf_counter() - w0) * 1e3 if N == 1 else 0.0)
+        if N > 1:
+            tt = torch.tensor([t_ms], dtype=torch.float64, device=dev); dist.all_reduce(tt, op=dist.ReduceOp.MAX); t_ms = float(tt[0])
+        return t_ms, each
+
+    # e2e: the steps queued through the asynchronous C ABI (PB_RENDER_ASYNC | PB_RENDER_HOST_BUFFERS: every step uploads
+    # the running sums from pinned host memory, renders, downloads the new sums; one pb_wait at the end).  Also
+    # reported: the same steps as synchronous calls, one at a time ("sync": exposed to host scheduling noise between
+    # calls - on shared boxes single steps took up to +50 ms).
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    e2e_step(0)
-    barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    w0 = time.perf_counter()
-    f0.record(stream)
-    e2e_each = []
-    for i in range(e2e_steps):
-        t_i = time.perf_counter()
-        e2e_step(args.warmup + i)
-        e2e_each.append(round((time.perf_counter() - t_i) * 1e3, 2))
-    f1.record(stream)
-    barrier()
-    e2e_ms = max(f0.elapsed_time(f1), (time.perf_counter() - w0) * 1e3 if N == 1 else 0.0)
-
-    if N > 1:
-        tt = torch.tensor([e2e_ms], dtype=torch.float64, device=dev); dist.all_reduce(tt, op=dist.ReduceOp.MAX); e2e_ms = float(tt[0])
+    e2e_ms, _ = e2e_run(True)
+    sync_ms, e2e_each = e2e_run(False)
     e2e_value = float(n_px) * S * e2e_steps * N / (e2e_ms * 1e-3) / 1e6
+    sync_value = float(n_px) * S * e2e_steps * N / (sync_ms * 1e-3) / 1e6
     h2d = n_px * 16 + C.sizeof(capi.RenderParams)
     d2h = n_px * 16
 
@@ -400,7 +412,8 @@ def product_main(args):
                            "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"},
                 "mrays_per_s": mrays, "rays_per_sample": (rays_c_all + rays_a_all) / samples,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "ms_each": e2e_each},
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "api": "pb_render(PB_RENDER_HOST_BUFFERS | PB_RENDER_ASYNC) x steps + pb_wait",
+                        "sync": {"value": sync_value, "ms_per_step": sync_ms / e2e_steps, "ms_each": e2e_each, "api": "pb_render(PB_RENDER_HOST_BUFFERS), one synchronous call per step"}},
                 "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
                 "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}
         line.update(extra)

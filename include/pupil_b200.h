@@ -116,10 +116,13 @@ enum {
                                     (same image; never the timed build)                          */
     PB_RENDER_STAGE_TIMING = 8u, /* CUDA events around every extend / connect launch: fills
                                     extend_ms / connect_ms / *_launches of pb_stats               */
-    PB_RENDER_ASYNC = 16u        /* device buffers only: return once the work is enqueued on the stream
-                                    (the reference's optixLaunch is asynchronous too, pass.h:79-86);
-                                    pb_wait / pb_get_stats synchronise and report the totals of all
-                                    renders enqueued since the last wait                           */
+    PB_RENDER_ASYNC = 16u        /* return once the work is enqueued on the stream (the reference's
+                                    optixLaunch is asynchronous too, pass.h:79-86); pb_wait /
+                                    pb_get_stats synchronise and report the totals of all renders
+                                    enqueued since the last wait.  With PB_RENDER_HOST_BUFFERS the
+                                    uploads / downloads are enqueued as well: the host buffers must stay
+                                    valid until pb_wait and should be pinned (pageable memory makes the
+                                    copies block the caller)                                        */
 };
 
 typedef struct pb_stats {

@@ -80,7 +80,6 @@ PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba
     if (!(p->flags & PB_RENDER_HOST_BUFFERS)) {
         return wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, s);   // synchronises unless PB_RENDER_ASYNC
     }
-    PB_REQUIRE(!(p->flags & PB_RENDER_ASYNC), "PB_RENDER_ASYNC needs device buffers");
     const auto h0 = std::chrono::steady_clock::now();
     // film staging lives in the context (no cudaMalloc / cudaFree - both synchronise the device - per call)
     if (c->stage_px < npx) {
@@ -101,6 +100,9 @@ PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba
         if (e == cudaSuccess && normal_rgb) e = cudaMemcpyAsync(normal_rgb, d_nrm, npx * 12, cudaMemcpyDeviceToHost, s);
         if (e != cudaSuccess) { c->err = std::string("render (host buffers): ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
         const auto h1 = std::chrono::steady_clock::now();
+        // PB_RENDER_ASYNC with host buffers: upload, kernels and download are all stream-ordered, so consecutive calls
+        // may share the staging film; the caller's buffers must stay valid (and should be pinned) until pb_wait
+        if (p->flags & PB_RENDER_ASYNC) return rc;
         const int rw = wavefront_wait(c);
         if (rc == PB_OK) rc = rw;
         if (getenv("PB_DEBUG_TIMING")) {

@@ -161,8 +161,12 @@ def test_async_renders_fold_into_one_wait(api):
         out = d.cpu().numpy()
     assert np.array_equal(out.view(np.uint32), ref.view(np.uint32))
     assert st["rays_closest"] == rays_sync and st["samples"] == 4 * w * h
-    with pytest.raises(capi.ApiError):      # host buffers cannot be asynchronous
-        g.render_into(capi.RenderParams(w, h, 6, 0, 1, 1, capi.RENDER_HOST_BUFFERS | capi.RENDER_ASYNC, 0), ref.copy())
+    # host buffers, asynchronous: upload / kernels / download are stream-ordered, one wait at the end
+    acc = torch.zeros((h, w, 4), dtype=torch.float32).pin_memory()
+    for first, flags in ((0, capi.RENDER_CLEAR), (2, 0)):
+        g.render_dev(capi.RenderParams(w, h, 6, first, 2, 1, flags | capi.RENDER_HOST_BUFFERS | capi.RENDER_ASYNC, 0), acc.data_ptr(), 0, 0, 0)
+    g.wait()
+    assert np.array_equal(acc.numpy().view(np.uint32), ref.view(np.uint32))
 
 
 def test_update_instance_rebuilds(api, oracle_api):
