@@ -11,6 +11,18 @@ using namespace pb;
         if (!(cond)) { c->err = (msg); return PB_ERR_INVALID; } \
     } while (0)
 
+// temporaries of the host-buffer entry points: released on every return path
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 1); }
+    template<class T> T* as() const { return static_cast<T*>(p); }
+};
+struct EventPair {
+    cudaEvent_t a = nullptr, b = nullptr;
+    ~EventPair() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+};
+
 static int trace_entry(pb_ctx* c, const pb_ray* rays, uint64_t n, void* out, int host, void* stream, bool any, bool counted) {
     if (!c) return PB_ERR_INVALID;
     if (!c->committed) { c->err = "scene not committed"; return PB_ERR_NOT_COMMITTED; }
@@ -18,13 +30,16 @@ static int trace_entry(pb_ctx* c, const pb_ray* rays, uint64_t n, void* out, int
     cudaSetDevice(c->device);
     cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
     const size_t out_bytes = any ? n : n * sizeof(pb_hit);
-    cudaEvent_t e0, e1;
-    PB_CUDA_TRY(c, cudaEventCreate(&e0)); PB_CUDA_TRY(c, cudaEventCreate(&e1));
+    EventPair ev;
+    PB_CUDA_TRY(c, cudaEventCreate(&ev.a)); PB_CUDA_TRY(c, cudaEventCreate(&ev.b));
+    const cudaEvent_t e0 = ev.a, e1 = ev.b;
     int rc = PB_OK;
     if (host) {
-        pb_ray* d_rays = nullptr; void* d_out = nullptr;
-        PB_CUDA_TRY(c, cudaMalloc(&d_rays, (n ? n : 1) * sizeof(pb_ray)));
-        PB_CUDA_TRY(c, cudaMalloc(&d_out, out_bytes ? out_bytes : 1));
+        DevBuf b_rays, b_out;
+        PB_CUDA_TRY(c, b_rays.alloc(n * sizeof(pb_ray)));
+        PB_CUDA_TRY(c, b_out.alloc(out_bytes));
+        pb_ray* d_rays = b_rays.as<pb_ray>();
+        void* d_out = b_out.p;
         PB_CUDA_TRY(c, cudaMemcpyAsync(d_rays, rays, n * sizeof(pb_ray), cudaMemcpyHostToDevice, s));
         cudaEventRecord(e0, s);
         rc = trace_rays(c, d_rays, n, any ? nullptr : (pb_hit*)d_out, any ? (uint8_t*)d_out : nullptr, any, counted, s);
@@ -34,7 +49,6 @@ static int trace_entry(pb_ctx* c, const pb_ray* rays, uint64_t n, void* out, int
             if (e == cudaSuccess) e = cudaStreamSynchronize(s);
             if (e != cudaSuccess) { c->err = std::string("trace (host buffers): ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
         }
-        cudaFree(d_rays); cudaFree(d_out);
     } else {
         cudaEventRecord(e0, s);
         rc = trace_rays(c, rays, n, any ? nullptr : (pb_hit*)out, any ? (uint8_t*)out : nullptr, any, counted, s);
@@ -50,7 +64,6 @@ static int trace_entry(pb_ctx* c, const pb_ray* rays, uint64_t n, void* out, int
         c->stats.last_trace_ms = ms;
         if (any) c->stats.rays_any = n; else c->stats.rays_closest = n;
     }
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
     return rc;
 }
 
@@ -124,15 +137,15 @@ PB_API int pb_resolve(pb_ctx* c, const float* sum, float* frame, uint32_t n, int
         PB_CUDA_TRY(c, cudaStreamSynchronize(s));
         return PB_OK;
     }
-    float *d_a = nullptr, *d_b = nullptr;
-    PB_CUDA_TRY(c, cudaMalloc(&d_a, (size_t)n * 16)); PB_CUDA_TRY(c, cudaMalloc(&d_b, (size_t)n * 16));
+    DevBuf b_a, b_b;
+    PB_CUDA_TRY(c, b_a.alloc((size_t)n * 16)); PB_CUDA_TRY(c, b_b.alloc((size_t)n * 16));
+    float *d_a = b_a.as<float>(), *d_b = b_b.as<float>();
     PB_CUDA_TRY(c, cudaMemcpyAsync(d_a, sum, (size_t)n * 16, cudaMemcpyHostToDevice, s));
     int rc = resolve_frame(c, d_a, d_b, n, s);
     if (rc == PB_OK) {
         PB_CUDA_TRY(c, cudaMemcpyAsync(frame, d_b, (size_t)n * 16, cudaMemcpyDeviceToHost, s));
         PB_CUDA_TRY(c, cudaStreamSynchronize(s));
     }
-    cudaFree(d_a); cudaFree(d_b);
     return rc;
 }
 
@@ -147,17 +160,17 @@ PB_API int pb_tonemap(pb_ctx* c, const float* frame, uint8_t* rgba8, uint32_t n,
         PB_CUDA_TRY(c, cudaStreamSynchronize(s));
         return PB_OK;
     }
-    float* d_a = nullptr;
-    uint8_t* d_b = nullptr;
-    PB_CUDA_TRY(c, cudaMalloc(&d_a, (size_t)n * 16 + 16));
-    cudaError_t e = cudaMalloc(&d_b, (size_t)n * 4 + 4);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_a, frame, (size_t)n * 16, cudaMemcpyHostToDevice, s);
+    DevBuf b_a, b_b;
+    PB_CUDA_TRY(c, b_a.alloc((size_t)n * 16));
+    PB_CUDA_TRY(c, b_b.alloc((size_t)n * 4));
+    float* d_a = b_a.as<float>();
+    uint8_t* d_b = b_b.as<uint8_t>();
+    cudaError_t e = cudaMemcpyAsync(d_a, frame, (size_t)n * 16, cudaMemcpyHostToDevice, s);
     int rc = e == cudaSuccess ? tonemap_frame(c, d_a, d_b, n, tone, gamma, s) : PB_ERR_CUDA;
     if (rc == PB_OK) {
         e = cudaMemcpyAsync(rgba8, d_b, (size_t)n * 4, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     }
-    cudaFree(d_a); cudaFree(d_b);
     if (e != cudaSuccess) { c->err = std::string("tonemap: ") + cudaGetErrorString(e); return PB_ERR_CUDA; }
     return rc;
 }

@@ -66,3 +66,30 @@ def test_empty_scene(hostsim_lib):
     rays = U.random_rays(100, 1)
     assert (hs_closest(hostsim_lib, h, rays)["prim"] == capi.MISS).all()
     assert (hs_any(hostsim_lib, h, rays) == 0).all()
+
+
+@pytest.mark.parametrize("leaf_max,bottom_max", [(1, 0), (1, 8), (2, 8), (3, 8), (3, 24), (2, 16)])
+def test_tree_shape_knobs_do_not_change_results(hostsim_lib, oracle_api, leaf_max, bottom_max):
+    """PB_LEAF_MAX / PB_BOTTOM_MAX (primitives per leaf slot, size of the subtrees collapsed into one bottom node)
+    change the 8-wide tree, never the hits: the intersection contract is tree independent."""
+    pos, idx, sph = U.random_soup(4000, 60, 11)
+    o = pyoracle.OracleContext(oracle_api)
+    U.oracle_scene(o, pos, idx, sph)
+    rays = U.random_rays(6000, 111)
+    rays["tmax"][::4] = 1.2
+    want = o.trace_closest_brute(rays)
+    hostsim_lib.hs_set_leaf_max.argtypes = [C.c_uint32]
+    hostsim_lib.hs_set_bottom_max.argtypes = [C.c_uint32]
+    hostsim_lib.hs_set_leaf_max(leaf_max)
+    hostsim_lib.hs_set_bottom_max(bottom_max)
+    try:
+        h = hs_build(hostsim_lib, pos, idx, sph)
+        got = hs_closest(hostsim_lib, h, rays)
+        assert np.array_equal(got["prim"], want["prim"])
+        hit = want["prim"] != capi.MISS
+        assert np.array_equal(got["t"][hit].view(np.uint32), want["t"][hit].view(np.uint32))
+        assert np.array_equal(hs_any(hostsim_lib, h, rays) != 0, hit)
+        hostsim_lib.hs_destroy(h)
+    finally:
+        hostsim_lib.hs_set_leaf_max(2)
+        hostsim_lib.hs_set_bottom_max(8)
