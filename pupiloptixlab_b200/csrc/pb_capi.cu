@@ -31,6 +31,7 @@ PB_API int pb_create(pb_ctx** out, int device) {
     cudaDeviceProp prop;
     PB_CUDA_TRY(c, cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
+    if (const char* e = getenv("PB_PRIM_ITERS")) { int v = atoi(e); if (v >= 1) c->prim_iters = (uint32_t)v; }
     if (const char* e = getenv("PB_PRIM_BATCH")) { int v = atoi(e); if (v >= 1 && v <= 32) c->prim_batch = (uint32_t)v; }
     if (const char* e = getenv("PB_LEAF_MAX")) { int v = atoi(e); if (v >= 1 && v <= 3) c->leaf_max = (uint32_t)v; }
     if (const char* e = getenv("PB_BOTTOM_MAX")) { int v = atoi(e); if (v >= 0 && v <= 24) c->bottom_max = (uint32_t)v; }

@@ -70,12 +70,13 @@ struct pb_ctx {
     int sm_count = 148;
     uint32_t leaf_max = 2;               // primitives per leaf slot (PB_LEAF_MAX, 1..3)
     uint32_t bottom_max = 8;             // BVH collapse: subtrees up to this size become one wide node (PB_BOTTOM_MAX)
+    uint32_t prim_iters = 0xFFFFFFFFu;   // PB_PRIM_ITERS
     uint32_t prim_batch = 8;             // lanes holding primitives before a warp runs its primitive tests (PB_PRIM_BATCH)
     uint32_t refill = 20;                // dynamic-fetch threshold (PB_REFILL overrides, tuning only)
     pb_stats stats{};
 
     pb::TraceScene trace_scene() const {
-        return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill, prim_batch, 0x47000000u};
+        return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill, prim_batch, 0x47000000u, prim_iters};
     }
 };
 

@@ -30,6 +30,7 @@ struct TraceScene {
     uint32_t refill;      // refill idle lanes when fewer than this many lanes of a warp hold a ray
     uint32_t prim_batch;  // run the primitive tests once this many lanes of a warp hold primitives
     uint32_t k47;         // 0x47000000 (see byte_f)
+    uint32_t prim_iters;  // primitives a lane tests per primitive phase; the rest waits for the next batch
 };
 
 struct Hit { float t, u, v; uint32_t prim; uint32_t obj; };
@@ -214,6 +215,7 @@ struct Traversal {
         const bool do_prims = true;
 #endif
         if (has_p && do_prims) {
+            uint32_t iters = sc.prim_iters;
             do {
                 const int i = lo_bit(P.y);
                 P.y &= P.y - 1u;
@@ -227,7 +229,7 @@ struct Traversal {
                     if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); P.y = 0u; return true; }
                     if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); }
                 }
-            } while (P.y);
+            } while (P.y && --iters);
         }
         if (alive && P.y == 0u && !(G.y & 0xff000000u)) {
             if (st.sp == 0) return true;

@@ -18,11 +18,15 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 
-def bounce_rays(rays, hits, seed=1):
+def bounce_rays(rays, hits, seed=1, target=0):
     """One cosine-sampled bounce ray from every primary hit (geometric normal from the hit triangle is not
-    needed for a ray SET: the hemisphere is oriented around +Y flipped against the incoming ray)."""
+    needed for a ray SET: the hemisphere is oriented around +Y flipped against the incoming ray).
+    `target` > number of hits: further bounce rays (new directions) from the same hit points until the set
+    holds `target` rays (C3 asks for as many incoherent rays as primary rays; only ~1/3 of those hit)."""
     from pupiloptixlab_b200 import capi
-    hit = hits["prim"] != capi.MISS
+    hit = np.flatnonzero(hits["prim"] != capi.MISS)
+    if target > len(hit) > 0:
+        hit = np.resize(hit, target)                 # cyclic repetition of the hit list
     r, h = rays[hit], hits[hit]
     n = len(r)
     rng = np.random.RandomState(seed)
@@ -51,8 +55,10 @@ def morton_order(rays, lo=-1.0, hi=1.0):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mesh", default="10M")
-    ap.add_argument("--rays", type=int, default=20_000_000)
+    ap.add_argument("--mesh", default="10M", help="1M | 10M | 100M, or a comma list (primary rays are generated once)")
+    ap.add_argument("--rays", type=int, default=20_000_000, help="primary rays (C3: 100000000)")
+    ap.add_argument("--incoherent", type=int, default=0, help="size of the incoherent set (0 = one bounce ray per primary hit; C3: 100000000)")
+    ap.add_argument("--no-sorted", action="store_true", help="skip the origin-Morton-sorted variant of the incoherent set")
     ap.add_argument("--spheres", type=int, default=0)
     ap.add_argument("--check", type=int, default=0)
     ap.add_argument("--reps", type=int, default=5)
@@ -60,10 +66,6 @@ def main():
     import torch
     from pupiloptixlab_b200 import capi, scenes
     api = capi.load()
-    g = capi.Context(api, 0)
-    n = scenes.MESH_N[args.mesh]
-    mesh = scenes.displaced_mesh(n)
-    info = scenes.bench_scene(g, n, args.spheres, 1920, 1080, patchwork=False, mesh=mesh)
     side = int(np.sqrt(args.rays))
     fov_y = scenes.fov_x_to_y(45.0, side, side)
     s2c = scenes.perspective_sample_to_camera(fov_y, 1.0)
@@ -72,6 +74,21 @@ def main():
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
     dev = torch.device("cuda", 0)
     stream = torch.cuda.Stream(dev); torch.cuda.set_stream(stream)
+    for mesh_name in args.mesh.split(","):
+        one_mesh(args, mesh_name, prim, api, capi, scenes, torch, dev, stream, peak)
+
+
+def one_mesh(args, mesh_name, prim, api, capi, scenes, torch, dev, stream, peak):
+    g = capi.Context(api, 0)
+    n = scenes.MESH_N[mesh_name]
+    t0 = time.time()
+    mesh = scenes.displaced_mesh(n)
+    t1 = time.time()
+    info = scenes.bench_scene(g, n, args.spheres, 1920, 1080, patchwork=False, mesh=mesh)
+    st0 = g.stats()
+    print(json.dumps({"mesh": mesh_name, "n_tris": info["n_tris"], "mesh_gen_s": round(t1 - t0, 1), "upload_commit_s": round(time.time() - t1, 1),
+                      "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"],
+                      "build_mtris_per_s": info["n_tris"] / st0["build_ms"] / 1e3 if st0["build_ms"] else None}), flush=True)
 
     def run(name, rays, any_hit=False):
         d_r = torch.from_numpy(rays.view(np.float32).reshape(-1, 8)).to(dev)
@@ -88,23 +105,30 @@ def main():
         g._ck(cnt_fn(g.h, d_r.data_ptr(), len(rays), d_h.data_ptr(), 0, stream.cuda_stream), "counted")
         st = g.stats()
         b = (32 + (1 if any_hit else 16)) + (80.0 * st["node_visits"] + 48.0 * st["prim_tests_tri"] + 32.0 * st["prim_tests_sphere"]) / len(rays)
-        out = {"set": name, "kernel": "k_trace<any>" if any_hit else "k_trace<closest>", "n_rays": len(rays), "mesh": args.mesh, "n_tris": info["n_tris"],
+        out = {"set": name, "kernel": "k_trace<any>" if any_hit else "k_trace<closest>", "n_rays": len(rays), "mesh": mesh_name, "n_tris": info["n_tris"],
                "spheres": args.spheres, "ms": t, "mrays_per_s": len(rays) / t / 1e3, "bytes_per_ray": b,
                "nodes_per_ray": st["node_visits"] / len(rays), "tris_per_ray": st["prim_tests_tri"] / len(rays),
                "roofline": {"bound": "hbm", "achieved": len(rays) * b / (t * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                             "frac": len(rays) * b / (t * 1e-3) / 1e9 / peak}}
         print(json.dumps(out), flush=True)
         res = d_h.cpu().numpy()
+        del d_r, d_h
         return res.view(capi.HIT_DTYPE).reshape(-1) if not any_hit else res
 
     hp = run("coherent primary", prim)
-    inc = bounce_rays(prim, hp)
+    inc = bounce_rays(prim, hp, target=args.incoherent)
     rng = np.random.RandomState(5)
     inc = inc[rng.permutation(len(inc))]            # queue order of a wavefront after compaction: unordered
     hi = run("incoherent bounce (unordered)", inc)
-    run("incoherent bounce (unordered), any-hit", inc, any_hit=True)
-    inc_s = inc[morton_order(inc)]
-    run("incoherent bounce (origin-Morton sorted)", inc_s)
+    occ = run("incoherent bounce (unordered), any-hit", inc, any_hit=True)
+    # size-independent property: "some accepted hit exists" == "the closest hit exists", for every ray
+    print(json.dumps({"check": "any-hit == (closest-hit found)", "mesh": mesh_name, "rays": len(inc),
+                      "mismatches": int(((hi["prim"] != capi.MISS) != (occ != 0)).sum())}), flush=True)
+    del occ
+    if not args.no_sorted:
+        inc_s = inc[morton_order(inc)]
+        run("incoherent bounce (origin-Morton sorted)", inc_s)
+        del inc_s
     if args.check:
         from oracle import pyoracle
         o = pyoracle.OracleContext(pyoracle.load())
@@ -115,7 +139,9 @@ def main():
             bad = int((want["prim"] != got["prim"][sel]).sum())
             hit = want["prim"] != capi.MISS
             bad_t = int((want["t"][hit].view(np.uint32) != got["t"][sel][hit].view(np.uint32)).sum())
-            print(json.dumps({"check": name, "rays": args.check, "id_mismatches": bad, "t_mismatches": bad_t, "hit_fraction": float(hit.mean())}), flush=True)
+            print(json.dumps({"check": name, "mesh": mesh_name, "rays": args.check, "id_mismatches": bad, "t_mismatches": bad_t, "hit_fraction": float(hit.mean())}), flush=True)
+        del o
+    del g
 
 
 if __name__ == "__main__":

@@ -121,7 +121,7 @@ void hs_counters(HS* h, unsigned long long* out) { out[0] = h->cnt.nodes; out[1]
 
 static TraceScene scene_of(HS* h) {
     return TraceScene{reinterpret_cast<const U4*>(h->nodes.data()), reinterpret_cast<const V4*>(h->prims_out.data()),
-                      h->objs.data(), h->delta, (uint32_t)h->nodes.size(), 32u, 1u, 0x47000000u};
+                      h->objs.data(), h->delta, (uint32_t)h->nodes.size(), 32u, 1u, 0x47000000u, 0xFFFFFFFFu};
 }
 void hs_trace_closest(HS* h, const float* rays, uint64_t n, float* hits /* t,u,v,prim bits */) {
     TraceScene sc = scene_of(h);
