@@ -114,6 +114,23 @@ inline float bias_lo(float, float b) { return b; }
 inline float bias_hi(float, float b) { return b; }
 #endif
 
+#ifndef PB_NODE_FMA2
+#define PB_NODE_FMA2 1
+#endif
+#if defined(__CUDA_ARCH__)
+// (q0, q1) * a + b on both halves with one FFMA2 (fma.rn.f32x2, sm_100+)
+PB_D float2 fma2(float q0, float q1, float2 a, float2 b) {
+    unsigned long long q, aa, bb, r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(q) : "f"(q0), "f"(q1));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(aa) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(b.x), "f"(b.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(q), "l"(aa), "l"(bb));
+    float2 o;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(o.x), "=f"(o.y) : "l"(r));
+    return o;
+}
+#endif
+
 // hit mask of one node for this ray: bits 24..31 inner children (octant ordered), bits 0..23 prims
 PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3, const U4& n4, V3 o, const RayPre& pre,
                          uint32_t octinv, float tmin, float tmax, uint32_t k47) {
@@ -131,6 +148,10 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
     const bool nx = pre.id.x < 0.f, ny = pre.id.y < 0.f, nz = pre.id.z < 0.f;
     const uint32_t octinv4 = octinv * 0x01010101u;
     uint32_t mask = 0;
+#if defined(__CUDA_ARCH__) && PB_NODE_FMA2
+    const float2 ax2 = {ax, ax}, ay2 = {ay, ay}, az2 = {az, az};
+    const float2 bnx2 = {bnx, bnx}, bfx2 = {bfx, bfx}, bny2 = {bny, bny}, bfy2 = {bfy, bfy}, bnz2 = {bnz, bnz}, bfz2 = {bfz, bfz};
+#endif
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
         const uint32_t meta4 = half ? n1.w : n1.z;
@@ -144,6 +165,27 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
         const uint32_t qnx = nx ? hx : lx, qfx = nx ? lx : hx;
         const uint32_t qny = ny ? hy : ly, qfy = ny ? ly : hy;
         const uint32_t qnz = nz ? hz : lz, qfz = nz ? lz : hz;
+#if defined(__CUDA_ARCH__) && PB_NODE_FMA2
+        // two children per instruction: sm_100 packed fp32 FMA (FFMA2, one issue slot for both halves; same rn
+        // rounding as FFMA, so the hit mask is bit-identical).  The kernel is bound by issue slots, not by the FMA pipe.
+#define PB_CHILD2(J, K)                                                                                          \
+        {                                                                                                        \
+            const float2 tnx = fma2(byte_f<J>(qnx, k47), byte_f<K>(qnx, k47), ax2, bnx2);                        \
+            const float2 tfx = fma2(byte_f<J>(qfx, k47), byte_f<K>(qfx, k47), ax2, bfx2);                        \
+            const float2 tny = fma2(byte_f<J>(qny, k47), byte_f<K>(qny, k47), ay2, bny2);                        \
+            const float2 tfy = fma2(byte_f<J>(qfy, k47), byte_f<K>(qfy, k47), ay2, bfy2);                        \
+            const float2 tnz = fma2(byte_f<J>(qnz, k47), byte_f<K>(qnz, k47), az2, bnz2);                        \
+            const float2 tfz = fma2(byte_f<J>(qfz, k47), byte_f<K>(qfz, k47), az2, bfz2);                        \
+            const float tn0 = fmaxf(fmaxf(tnx.x, tny.x), fmaxf(tnz.x, tmin)), tn1 = fmaxf(fmaxf(tnx.y, tny.y), fmaxf(tnz.y, tmin)); \
+            const float tf0 = fminf(fminf(tfx.x, tfy.x), fminf(tfz.x, tmax)), tf1 = fminf(fminf(tfx.y, tfy.y), fminf(tfz.y, tmax)); \
+            const uint32_t bits0 = byte_u<J>(child_bits4) << ((bit_index4 >> (8 * J)) & 0xffu);                 \
+            const uint32_t bits1 = byte_u<K>(child_bits4) << ((bit_index4 >> (8 * K)) & 0xffu);                 \
+            mask |= tn0 <= tf0 ? bits0 : 0u;                                                                     \
+            mask |= tn1 <= tf1 ? bits1 : 0u;                                                                     \
+        }
+        PB_CHILD2(0, 1) PB_CHILD2(2, 3)
+#undef PB_CHILD2
+#else
 #define PB_CHILD(J)                                                                                              \
         {                                                                                                        \
             const float tnx = f_fma(byte_f<J>(qnx, k47), ax, bnx), tfx = f_fma(byte_f<J>(qfx, k47), ax, bfx);   \
@@ -156,6 +198,7 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
         }
         PB_CHILD(0) PB_CHILD(1) PB_CHILD(2) PB_CHILD(3)
 #undef PB_CHILD
+#endif
     }
     return mask;
 }
