@@ -155,9 +155,8 @@ PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t
     }
     nd.ex = (uint8_t)ex; nd.ey = (uint8_t)ey; nd.ez = (uint8_t)ez;
     const double sx = u2f(ex << 23), sy = u2f(ey << 23), sz = u2f(ez << 23);
-    uint32_t imask = 0;
+    uint32_t imask = 0, pmask = 0;
     for (int s = 0; s < 8; ++s) {
-        nd.meta[s] = 0;
         nd.qlox[s] = nd.qloy[s] = nd.qloz[s] = 0;
         nd.qhix[s] = nd.qhiy[s] = nd.qhiz[s] = 0;
     }
@@ -173,18 +172,18 @@ PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t
         nd.qhix[s] = qhi(chi[k].x, lo.x, sx); nd.qhiy[s] = qhi(chi[k].y, lo.y, sy); nd.qhiz[s] = qhi(chi[k].z, lo.z, sz);
         if (!(ch[k] & kLeafFlag)) {
             imask |= 1u << s;
-            nd.meta[s] = (uint8_t)(0x20u | (24u + (uint32_t)s));
             c.next_work[off_inner + inner_rank] = {ch[k], c.next_wide_base + off_inner + inner_rank};
             ++inner_rank;
         } else {
             const uint32_t cnt = range_count(ch[k]), first = range_first(ch[k]);
-            nd.meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | prim_off);
+            pmask |= ((1u << cnt) - 1u) << (3 * s);
             for (uint32_t j = 0; j < cnt; ++j)
                 c.prims_out[c.prim_cursor + off_prims + prim_off + j] = b.prims_in[b.order[first + j]];
             prim_off += cnt;
         }
     }
     nd.imask = (uint8_t)imask;
+    nd.pmask = pmask; nd.spare = 0u;
     nd.child_base = c.next_wide_base + off_inner;
     nd.prim_base = c.prim_cursor + off_prims;
     c.nodes[c.work[w].wide_index] = nd;

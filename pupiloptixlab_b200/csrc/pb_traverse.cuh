@@ -118,12 +118,12 @@ inline float bias_hi(float, float b) { return b; }
 #define PB_NODE_FMA2 1
 #endif
 #if defined(__CUDA_ARCH__)
-// (q0, q1) * a + b on both halves with one FFMA2 (fma.rn.f32x2, sm_100+)
-PB_D float2 fma2(float q0, float q1, float2 a, float2 b) {
+// (q0, q1) * a + b on both halves with one FFMA2 (fma.rn.f32x2, sm_100+; ptxas broadcasts the scalar operands)
+PB_D float2 fma2(float q0, float q1, float a, float b) {
     unsigned long long q, aa, bb, r;
     asm("mov.b64 %0, {%1, %2};" : "=l"(q) : "f"(q0), "f"(q1));
-    asm("mov.b64 %0, {%1, %2};" : "=l"(aa) : "f"(a.x), "f"(a.y));
-    asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(aa) : "f"(a));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(bb) : "f"(b));
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(q), "l"(aa), "l"(bb));
     float2 o;
     asm("mov.b64 {%0, %1}, %2;" : "=f"(o.x), "=f"(o.y) : "l"(r));
@@ -131,57 +131,75 @@ PB_D float2 fma2(float q0, float q1, float2 a, float2 b) {
 }
 #endif
 
-// hit mask of one node for this ray: bits 24..31 inner children (octant ordered), bits 0..23 prims
-PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3, const U4& n4, V3 o, const RayPre& pre,
-                         uint32_t octinv, float tmin, float tmax, uint32_t k47) {
-    // n0 = px py pz [ex ey ez imask]; n1 = child_base prim_base meta[0..3] meta[4..7]
+// Per-ray constants of the octant permutation, packed in one register: byte 0 = octinv, bytes 1..3 = the
+// delta-swap masks of the three stages (0x55 / 0x33 / 0x0f when the matching bit of octinv is set, else 0).
+// Inner-child hits are collected in slot order (bit 24 + slot) and moved to bit 24 + (slot ^ octinv) by three
+// conditional delta swaps IN the high byte of the hit word, so that hi_bit() visits the children front to
+// back (Ylitie et al. 2017, octant order).
+PB_HD uint32_t oct_perm(uint32_t octinv) {
+    return octinv | ((octinv & 1u) ? 0x5500u : 0u) | ((octinv & 2u) ? 0x330000u : 0u) | ((octinv & 4u) ? 0x0f000000u : 0u);
+}
+#if defined(__CUDA_ARCH__)
+template<int B> PB_D uint32_t byte_to_top(uint32_t w) { return __byte_perm(w, 0u, 0x0444u | (B << 12)); }   // byte B -> byte 3, rest 0
+// bytes (a0, a1, a2, b3) / (a.B0, b.B1, b.B2 ...) helpers for the group packing below
+PB_D uint32_t pack_p(uint32_t hits, uint32_t pm) { return __byte_perm(hits, pm, 0x6210); }        // hits[0..2], pm[2]
+PB_D uint32_t pack_g(uint32_t hits, uint32_t pm, uint32_t n0w) {                                   // imask, pm[0], pm[1], hits[3]
+    return __byte_perm(__byte_perm(n0w, pm, 0x0543), hits, 0x7210);
+}
+PB_D uint32_t unpack_pm(uint32_t gy, uint32_t py) { return __byte_perm(gy, py, 0x4721); }   // byte 3 = junk: callers mask below bit 24
+#else
+template<int B> inline uint32_t byte_to_top(uint32_t w) { return ((w >> (8 * B)) & 0xffu) << 24; }
+inline uint32_t pack_p(uint32_t hits, uint32_t pm) { return (hits & 0x00ffffffu) | ((pm >> 16) << 24); }
+inline uint32_t pack_g(uint32_t hits, uint32_t pm, uint32_t n0w) { return (hits & 0xff000000u) | ((pm & 0xffffu) << 8) | (n0w >> 24); }
+inline uint32_t unpack_pm(uint32_t gy, uint32_t py) { return ((gy >> 8) & 0xffffu) | ((py >> 24) << 16); }
+#endif
+PB_HD uint32_t delta_swap(uint32_t x, uint32_t m, int k) {
+    const uint32_t t = ((x >> k) ^ x) & m;
+    return x ^ t ^ (t << k);
+}
+
+// hit word of one node for this ray: bits 24..31 = inner children hit, in octant order; bits 0..23 = leaf slots hit
+// (3 bits per slot, masked by the node's pmask, i.e. one bit per primitive in slot order)
+PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3, const U4& n4, V3 o, V3 id,
+                         uint32_t op, float tmin, float tmax, uint32_t k47) {
+    // n0 = px py pz [ex ey ez imask]; n1 = child_base prim_base pmask spare
     // n2 = qlox[0..7] qloy[0..7]; n3 = qloz[0..7] qhix[0..7]; n4 = qhiy[0..7] qhiz[0..7]
     const uint32_t e = n0.w;
     const float sx = u2f((e & 0xffu) << 23), sy = u2f(((e >> 8) & 0xffu) << 23), sz = u2f(((e >> 16) & 0xffu) << 23);
-    const float ax = f_mul(plane_scale(sx), pre.id.x), ay = f_mul(plane_scale(sy), pre.id.y), az = f_mul(plane_scale(sz), pre.id.z);
-    const float bx = f_mul(f_sub(u2f(n0.x), o.x), pre.id.x);
-    const float by = f_mul(f_sub(u2f(n0.y), o.y), pre.id.y);
-    const float bz = f_mul(f_sub(u2f(n0.z), o.z), pre.id.z);
+    const float ax = f_mul(plane_scale(sx), id.x), ay = f_mul(plane_scale(sy), id.y), az = f_mul(plane_scale(sz), id.z);
+    const float bx = f_mul(f_sub(u2f(n0.x), o.x), id.x);
+    const float by = f_mul(f_sub(u2f(n0.y), o.y), id.y);
+    const float bz = f_mul(f_sub(u2f(n0.z), o.z), id.z);
     const float bnx = bias_lo(ax, bx), bfx = bias_hi(ax, bx);
     const float bny = bias_lo(ay, by), bfy = bias_hi(ay, by);
     const float bnz = bias_lo(az, bz), bfz = bias_hi(az, bz);
-    const bool nx = pre.id.x < 0.f, ny = pre.id.y < 0.f, nz = pre.id.z < 0.f;
-    const uint32_t octinv4 = octinv * 0x01010101u;
-    uint32_t mask = 0;
-#if defined(__CUDA_ARCH__) && PB_NODE_FMA2
-    const float2 ax2 = {ax, ax}, ay2 = {ay, ay}, az2 = {az, az};
-    const float2 bnx2 = {bnx, bnx}, bfx2 = {bfx, bfx}, bny2 = {bny, bny}, bfy2 = {bfy, bfy}, bnz2 = {bnz, bnz}, bfz2 = {bfz, bfz};
-#endif
+    const bool nx = id.x < 0.f, ny = id.y < 0.f, nz = id.z < 0.f;
+    uint32_t acc = 0;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
-        const uint32_t meta4 = half ? n1.w : n1.z;
-        // per child byte (Ylitie et al. 2017, listing 1): inner children have bits 3 and 4 of meta set
-        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-        const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;   // inner: 24 + (slot ^ octinv)
-        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;                        // inner: 1, leaf: unary count, empty: 0
         const uint32_t lx = half ? n2.y : n2.x, ly = half ? n2.w : n2.z, lz = half ? n3.y : n3.x;
         const uint32_t hx = half ? n3.w : n3.z, hy = half ? n4.y : n4.x, hz = half ? n4.w : n4.z;
         const uint32_t qnx = nx ? hx : lx, qfx = nx ? lx : hx;
         const uint32_t qny = ny ? hy : ly, qfy = ny ? ly : hy;
         const uint32_t qnz = nz ? hz : lz, qfz = nz ? lz : hz;
+        // slot S hit: its three leaf bits and its inner bit, one constant; pmask / imask keep what exists
+#define PB_SLOT_BITS(S) ((7u << (3 * (S))) | (1u << (24 + (S))))
 #if defined(__CUDA_ARCH__) && PB_NODE_FMA2
-        // two children per instruction: sm_100 packed fp32 FMA (FFMA2, one issue slot for both halves; same rn
-        // rounding as FFMA, so the hit mask is bit-identical).  The kernel is bound by issue slots, not by the FMA pipe.
+        // two children per instruction: sm_100 packed fp32 FMA (FFMA2, one issue slot for both halves, scalar
+        // operands broadcast; same rn rounding as FFMA, so the hit word is bit-identical).  The kernel is bound by
+        // issue slots, not by the FMA pipe.
 #define PB_CHILD2(J, K)                                                                                          \
         {                                                                                                        \
-            const float2 tnx = fma2(byte_f<J>(qnx, k47), byte_f<K>(qnx, k47), ax2, bnx2);                        \
-            const float2 tfx = fma2(byte_f<J>(qfx, k47), byte_f<K>(qfx, k47), ax2, bfx2);                        \
-            const float2 tny = fma2(byte_f<J>(qny, k47), byte_f<K>(qny, k47), ay2, bny2);                        \
-            const float2 tfy = fma2(byte_f<J>(qfy, k47), byte_f<K>(qfy, k47), ay2, bfy2);                        \
-            const float2 tnz = fma2(byte_f<J>(qnz, k47), byte_f<K>(qnz, k47), az2, bnz2);                        \
-            const float2 tfz = fma2(byte_f<J>(qfz, k47), byte_f<K>(qfz, k47), az2, bfz2);                        \
+            const float2 tnx = fma2(byte_f<J>(qnx, k47), byte_f<K>(qnx, k47), ax, bnx);                          \
+            const float2 tfx = fma2(byte_f<J>(qfx, k47), byte_f<K>(qfx, k47), ax, bfx);                          \
+            const float2 tny = fma2(byte_f<J>(qny, k47), byte_f<K>(qny, k47), ay, bny);                          \
+            const float2 tfy = fma2(byte_f<J>(qfy, k47), byte_f<K>(qfy, k47), ay, bfy);                          \
+            const float2 tnz = fma2(byte_f<J>(qnz, k47), byte_f<K>(qnz, k47), az, bnz);                          \
+            const float2 tfz = fma2(byte_f<J>(qfz, k47), byte_f<K>(qfz, k47), az, bfz);                          \
             const float tn0 = fmaxf(fmaxf(tnx.x, tny.x), fmaxf(tnz.x, tmin)), tn1 = fmaxf(fmaxf(tnx.y, tny.y), fmaxf(tnz.y, tmin)); \
             const float tf0 = fminf(fminf(tfx.x, tfy.x), fminf(tfz.x, tmax)), tf1 = fminf(fminf(tfx.y, tfy.y), fminf(tfz.y, tmax)); \
-            const uint32_t bits0 = byte_u<J>(child_bits4) << ((bit_index4 >> (8 * J)) & 0xffu);                 \
-            const uint32_t bits1 = byte_u<K>(child_bits4) << ((bit_index4 >> (8 * K)) & 0xffu);                 \
-            mask |= tn0 <= tf0 ? bits0 : 0u;                                                                     \
-            mask |= tn1 <= tf1 ? bits1 : 0u;                                                                     \
+            if (tn0 <= tf0) acc |= PB_SLOT_BITS(4 * half + J);                                                   \
+            if (tn1 <= tf1) acc |= PB_SLOT_BITS(4 * half + K);                                                   \
         }
         PB_CHILD2(0, 1) PB_CHILD2(2, 3)
 #undef PB_CHILD2
@@ -193,14 +211,18 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
             const float tnz = f_fma(byte_f<J>(qnz, k47), az, bnz), tfz = f_fma(byte_f<J>(qfz, k47), az, bfz);   \
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));                                           \
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));                                           \
-            const uint32_t bits = byte_u<J>(child_bits4) << ((bit_index4 >> (8 * J)) & 0xffu);                  \
-            mask |= tn <= tf ? bits : 0u;                                                                        \
+            if (tn <= tf) acc |= PB_SLOT_BITS(4 * half + J);                                                     \
         }
         PB_CHILD(0) PB_CHILD(1) PB_CHILD(2) PB_CHILD(3)
 #undef PB_CHILD
 #endif
+#undef PB_SLOT_BITS
     }
-    return mask;
+    acc &= n1.z | (n0.w & 0xff000000u);                       // pmask | imask << 24
+    acc = delta_swap(acc, byte_to_top<1>(op), 1);
+    acc = delta_swap(acc, byte_to_top<2>(op), 2);
+    acc = delta_swap(acc, op & 0xff000000u, 4);
+    return acc;
 }
 
 // Resumable traversal of one ray: begin() once, then step() until it returns true.  One step = at
@@ -215,17 +237,20 @@ template<bool ANY, bool COUNT>
 struct Traversal {
     V3 o, d;
     float tmin, tmax;   // tmax = the ray's own bound (ties on t need it; best.t only orders)
-    RayPre pre;
-    uint32_t octinv;
-    U2 G, P;            // pending node group / primitive group
+    V3 id;              // 1 / d (RayPre::id); RayPre::noid is re-derived in the primitive phase (3 registers less)
+    uint32_t op;        // oct_perm(octinv): octinv in the low byte
+    U2 G, P;            // pending node group / primitive group.  G.y = inner hits << 24 | pmask[0..15] << 8 | imask,
+                        // P.y = pmask[16..23] << 24 | primitive hits: the pmask of the node P came from rides in the spare
+                        // bits (primitive of hit bit i = P.x + popc(pmask & ((1 << i) - 1))); G on the stack carries stale
+                        // pmask bits that nothing reads
     Hit best;
 
     PB_HD void begin(const TraceScene& sc, V3 o_, V3 d_, float tmin_, float tmax_, LaneStack& st) {
         o = o_; d = d_; tmin = tmin_; tmax = tmax_;
         best.t = tmax_; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu; best.obj = 0xFFFFFFFFu;
-        pre = ray_pre(o, d);
+        id = ray_pre(o, d).id;
         const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
-        octinv = 7u - oct;
+        op = oct_perm(7u - oct);
         G = {0u, sc.n_nodes ? 0x80000000u : 0u};
         P = {0u, 0u};
         st.sp = 0;
@@ -234,23 +259,23 @@ struct Traversal {
 
     // returns true when the ray is finished (best holds the result); `alive` = this lane holds a ray
     PB_HD bool step(const TraceScene& sc, LaneStack& st, TraceCounters* cnt, bool alive) {
-        if (alive && P.y == 0u) {   // invariant: an alive lane without primitives has inner hits in G
+        if (alive && (P.y & 0x00ffffffu) == 0u) {   // invariant: an alive lane without primitives has inner hits in G
             const int bit = hi_bit(G.y);
             const uint32_t imask = G.y & 0xffu;
             G.y &= ~(1u << bit);
             if (G.y & 0xff000000u) st.push(G);
-            const uint32_t slot = ((uint32_t)bit - 24u) ^ octinv;
+            const uint32_t slot = (((uint32_t)bit - 24u) ^ op) & 7u;
             const uint32_t rel = (uint32_t)pop_cnt(imask & ((1u << slot) - 1u));
             const U4* np = sc.nodes + 5ull * (G.x + rel);
             const U4 n0 = ld_u4(np), n1 = ld_u4(np + 1), n2 = ld_u4(np + 2), n3 = ld_u4(np + 3), n4 = ld_u4(np + 4);
             if (COUNT) cnt->nodes++;
-            const uint32_t hits = node_hits(n0, n1, n2, n3, n4, o, pre, octinv, tmin, best.t, sc.k47);
+            const uint32_t hits = node_hits(n0, n1, n2, n3, n4, o, id, op, tmin, best.t, sc.k47);
             G.x = n1.x;
-            G.y = (hits & 0xff000000u) | (n0.w >> 24);
+            G.y = pack_g(hits, n1.z, n0.w);
             P.x = n1.y;
-            P.y = hits & 0x00ffffffu;
+            P.y = pack_p(hits, n1.z);
         }
-        const bool has_p = alive && P.y != 0u;
+        const bool has_p = alive && (P.y & 0x00ffffffu) != 0u;
 #if defined(__CUDA_ARCH__)
         const unsigned pm = __ballot_sync(0xFFFFFFFFu, has_p);
         const bool do_prims = (uint32_t)__popc(pm) >= sc.prim_batch || pm == __ballot_sync(0xFFFFFFFFu, alive);
@@ -259,10 +284,11 @@ struct Traversal {
 #endif
         if (has_p && do_prims) {
             uint32_t iters = sc.prim_iters;
+            const RayPre pre = {id, {-f_mul(o.x, id.x), -f_mul(o.y, id.y), -f_mul(o.z, id.z)}};   // == ray_pre(o, d), bit for bit
             do {
                 const int i = lo_bit(P.y);
                 P.y &= P.y - 1u;
-                const V4* pp = sc.prims + 3ull * (P.x + (uint32_t)i);
+                const V4* pp = sc.prims + 3ull * (P.x + (uint32_t)pop_cnt(unpack_pm(G.y, P.y) & ((1u << i) - 1u)));
                 PrimRec r;
                 r.a = ld_v4(pp); r.b = ld_v4(pp + 1); r.c = ld_v4(pp + 2);
                 if (COUNT) { if (f2u(r.c.w) == PRIM_TRI) cnt->tris++; else cnt->spheres++; }
@@ -272,9 +298,9 @@ struct Traversal {
                     if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); P.y = 0u; return true; }
                     if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); }
                 }
-            } while (P.y && --iters);
+            } while ((P.y & 0x00ffffffu) && --iters);
         }
-        if (alive && P.y == 0u && !(G.y & 0xff000000u)) {
+        if (alive && (P.y & 0x00ffffffu) == 0u && !(G.y & 0xff000000u)) {
             if (st.sp == 0) return true;
             G = st.pop();
         }

@@ -92,7 +92,9 @@ struct alignas(16) Node8 {
     uint8_t ex, ey, ez, imask; // per-axis exponent (biased, scale = 2^(e-127) as float bits e<<23), inner mask
     uint32_t child_base;       // index of the first inner child (children are contiguous, rank = popc)
     uint32_t prim_base;        // index of the first primitive referenced by leaf children
-    uint8_t meta[8];           // inner: 0b001sssss with sssss = 24 + slot; leaf: unary count <<5 | offset; empty 0
+    uint32_t pmask;            // leaf slots: 3 bits per slot (bits 3s..3s+2), unary primitive count (1, 3, 7); inner / empty: 0.
+                               // Primitive j of the node's range sits behind the j-th set bit (slot order).
+    uint32_t spare;
     uint8_t qlox[8], qloy[8], qloz[8];
     uint8_t qhix[8], qhiy[8], qhiz[8];
 };
