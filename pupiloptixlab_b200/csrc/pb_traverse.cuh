@@ -115,7 +115,7 @@ inline float bias_hi(float, float b) { return b; }
 #endif
 
 #ifndef PB_NODE_FMA2
-#define PB_NODE_FMA2 1
+#define PB_NODE_FMA2 0   // A/B on C4 (scripts/ab_node_test.sh): scalar FFMA 481.3 vs FFMA2 479.0 Msamples/s (the packing MOVs cost what the pairs save)
 #endif
 #if defined(__CUDA_ARCH__)
 // (q0, q1) * a + b on both halves with one FFMA2 (fma.rn.f32x2, sm_100+; ptxas broadcasts the scalar operands)

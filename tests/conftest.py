@@ -21,8 +21,7 @@ def oracle_api():
     return pyoracle.load()
 
 
-@pytest.fixture(scope="session")
-def hostsim_lib():
+def _build_hostsim():
     """g++ build of the kernels' per-thread bodies (tests/hostsim) — test harness only."""
     import ctypes
     d = os.path.join(ROOT, "tests", "hostsim")
@@ -32,5 +31,10 @@ def hostsim_lib():
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         fma = ["-mfma"] if "fma" in open("/proc/cpuinfo").read() else []
         subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", *fma, "-shared",
-                               "-Wno-unknown-pragmas", "-o", so, os.path.join(d, "hostsim.cpp")])
+                               "-Wno-unknown-pragmas", *os.environ.get("HS_EXTRA", "").split(), "-o", so, os.path.join(d, "hostsim.cpp")])
     return ctypes.CDLL(so)
+
+
+@pytest.fixture(scope="session")
+def hostsim_lib():
+    return _build_hostsim()
