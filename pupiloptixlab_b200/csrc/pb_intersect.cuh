@@ -112,7 +112,15 @@ PB_HD bool prim_accept(const PrimRec& r, const ObjRec* objs, V3 o, V3 d, const R
         if (!tri_test(o, d, tmin, tmax, {r.a.x, r.a.y, r.a.z}, {r.b.x, r.b.y, r.b.z}, {r.c.x, r.c.y, r.c.z}, t, u, v)) return false;
     } else {
         u = 0.f; v = 0.f;
-        if (!sphere_test(o, d, tmin, tmax, objs[f2u(r.b.w)].Minv, t)) return false;
+#if defined(__CUDA_ARCH__)
+        // the 12 floats of Minv as 3 x LDG.128 (offset 48 of a 128 B record) instead of 12 scalar loads
+        const float4* mp = reinterpret_cast<const float4*>(objs[f2u(r.b.w)].Minv);
+        const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), m2 = __ldg(mp + 2);
+        const float Minv[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
+#else
+        const float* Minv = objs[f2u(r.b.w)].Minv;
+#endif
+        if (!sphere_test(o, d, tmin, tmax, Minv, t)) return false;
     }
     return N <= t && t <= F;
 }
