@@ -172,6 +172,10 @@ def cpu_leg(mesh_tag, mesh, seconds_target, steps, warmup, want_line):
     if o.has_reference():
         o.set_backend(1)
         kind = "reference"
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm uses every host core it may run on
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and int(api._max_threads()) < avail:
+        api._set_threads(avail)
     cores = int(api._max_threads())
     info, mesh = build_scene(o, mesh_tag, mesh)
     # probe, then the largest film (same camera, same scene) whose 1-spp frame fits the time budget
@@ -210,7 +214,7 @@ def reference_main(args):
             "mrays_per_s": base["mrays_per_s"], "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -417,11 +421,32 @@ def product_main(args):
                 "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
                 "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}
         line.update(extra)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if N > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+_JSON_FD = None
+
+
+def claim_stdout():
+    """stdout carries the ONE JSON line and nothing else: from here on fd 1 points at stderr, so that libraries which
+    printf to it (NCCL's version banner under NCCL_DEBUG=VERSION ignores NCCL_DEBUG_FILE) cannot get in front of it."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
@@ -443,6 +468,7 @@ def main():
         WORKLOAD = WORKLOAD.replace("C4:", "C5:").replace("1920x1080", "3840x2160")
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
+        claim_stdout()
         return reference_main(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus != world and world == 1 and args.gpus > 1:
@@ -450,6 +476,7 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd)
+    claim_stdout()
     return product_main(args)
 
 
