@@ -134,11 +134,29 @@ __global__ void k_prepare(WfState s, int cur, uint32_t set_cur_count, int set) {
 __global__ void k_after_shade(WfState s) { s.totals[1] += s.cnt[C_SHADOW]; }
 __global__ void k_set_frame0(WfState s, uint32_t frame0) { s.cnt[C_FRAME0] = frame0; }
 
+// Path j of a frame -> pixel.  A frame is walked in strips of PB_TILE_ROWS rows, column by column, so that 32 consecutive
+// paths (one warp of every stage, one refill of the traversal loop) cover an 8 x 4 pixel block instead of a 32 x 1 row:
+// their primary rays share more nodes and their bounce rays start closer together.  A bijection for any film size (the
+// last strip just has fewer rows); seeds and sums are per pixel, so results do not depend on it.
+#ifndef PB_TILE_ROWS
+#define PB_TILE_ROWS 4u
+#endif
+__device__ __forceinline__ uint32_t path_pixel(uint32_t j, uint32_t w, uint32_t h) {
+    if (PB_TILE_ROWS <= 1u) return j;
+    const uint32_t strips = h / PB_TILE_ROWS, full = strips * PB_TILE_ROWS * w;
+    if (j < full) {
+        const uint32_t s = j / (PB_TILE_ROWS * w), q = j - s * PB_TILE_ROWS * w;
+        return (PB_TILE_ROWS * s + q % PB_TILE_ROWS) * w + q / PB_TILE_ROWS;
+    }
+    const uint32_t r = h - strips * PB_TILE_ROWS, q = j - full;
+    return (strips * PB_TILE_ROWS + q % r) * w + q / r;
+}
+
 // ---- generate: camera rays of K frames (main.cu:37-75) ----------------------------------------------
 __global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_t n_paths) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= n_paths) return;
-    const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
+    const uint32_t k = slot / sc.n_px, pixel = path_pixel(slot - k * sc.n_px, sc.width, sc.height);
     const uint32_t x = pixel % sc.width, y = pixel / sc.width;
     Rng rng;
     rng.init(pixel, s.cnt[C_FRAME0] + k * sc.stride);
@@ -289,8 +307,9 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
             int depth = (int)(fl & F_DEPTH_MASK);
             if (depth == 0) {  // primary hit: main.cu:87-101
                 if (emitter_index >= 0) radiance += emitter_radiance(sc.em.rec[emitter_index], geo.texcoord);
-                const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
+                const uint32_t k = slot / sc.n_px;
                 if (k == k_aov) {
+                    const uint32_t pixel = path_pixel(slot - k * sc.n_px, sc.width, sc.height);
                     if (albedo) { const V3 a = bsdf_albedo<MAT>(bsdf); albedo[3 * pixel] = a.x; albedo[3 * pixel + 1] = a.y; albedo[3 * pixel + 2] = a.z; }
                     if (normal) { normal[3 * pixel] = geo.normal.x; normal[3 * pixel + 1] = geo.normal.y; normal[3 * pixel + 2] = geo.normal.z; }
                 }
@@ -379,8 +398,9 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
         const uint32_t fl = __float_as_uint(ro4.w);
         const bool primary = (fl & F_DEPTH_MASK) == 0u;
         if (primary) {
-            const uint32_t k = slot / sc.n_px, pixel = slot - k * sc.n_px;
+            const uint32_t k = slot / sc.n_px;
             if (k == k_aov) {
+                const uint32_t pixel = path_pixel(slot - k * sc.n_px, sc.width, sc.height);
                 if (albedo) { albedo[3 * pixel] = 0.f; albedo[3 * pixel + 1] = 0.f; albedo[3 * pixel + 2] = 0.f; }
                 if (normal) { normal[3 * pixel] = 0.f; normal[3 * pixel + 1] = 0.f; normal[3 * pixel + 2] = 0.f; }
             }
@@ -402,12 +422,13 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
 }
 
 // ---- accumulate: frame-ordered sum of the K radiances of each pixel (main.cu:187-193 as sum/count) ----------
-__global__ void __launch_bounds__(256) k_accumulate(WfState s, float4* sum, uint32_t n_px, uint32_t k_count) {
-    const uint32_t pixel = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pixel >= n_px) return;
+__global__ void __launch_bounds__(256) k_accumulate(WfState s, float4* sum, uint32_t width, uint32_t height, uint32_t k_count) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x, n_px = width * height;
+    if (j >= n_px) return;
+    const uint32_t pixel = path_pixel(j, width, height);
     float4 a = sum[pixel];
     for (uint32_t k = 0; k < k_count; ++k) {
-        const float4 r = s.rec[(size_t)R_COUNT * ((size_t)k * n_px + pixel) + R_RAD];
+        const float4 r = s.rec[(size_t)R_COUNT * ((size_t)k * n_px + j) + R_RAD];
         a.x += r.x; a.y += r.y; a.z += r.z; a.w += 1.f;
     }
     sum[pixel] = a;
@@ -585,7 +606,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
                 mark(ev_con);
                 cur ^= 1;
             }
-            k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), n_px, kw);
+            k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), p->width, p->height, kw);
         };
         launches += 2u + 12u * std::max(1u, p->max_depth);
         cudaGraphExec_t exec = nullptr;
