@@ -107,6 +107,7 @@ struct WfScene {
     EmitterTable em;
     Camera cam;
     uint32_t width, height, n_px, max_depth;
+    uint32_t kw;             // frames in this wave (slot_to_kj)
     uint32_t stride;      // frame index step; the first frame of a wave is s.cnt[C_FRAME0] (set per wave, so that a
                           // captured wave graph can be replayed for any first_sample)
 };
@@ -152,11 +153,34 @@ __device__ __forceinline__ uint32_t path_pixel(uint32_t j, uint32_t w, uint32_t 
     return (strips * PB_TILE_ROWS + q % r) * w + q / r;
 }
 
+// Slot of a wave <-> (frame k of the wave, path j of the frame).  The frames of a wave are interleaved in groups of
+// PB_FRAME_GROUP paths: slots [g * G * K, (g + 1) * G * K) hold paths [g * G, (g + 1) * G) of all K frames, frame by frame,
+// so the rays in flight at any moment come from a K times smaller part of the film than with frame-major slots and
+// their leaves and primitives stay in L2.  Any film size (the last group is shorter); PB_FRAME_GROUP 0 = frame-major.
+#ifndef PB_FRAME_GROUP
+#define PB_FRAME_GROUP 256u   // C4, same box: frame-major 492.9, groups of 32 / 256 / 4096 paths 494.5 / 495.2 / 495.1 Msamples/s
+#endif
+__device__ __forceinline__ void slot_to_kj(uint32_t slot, uint32_t n_px, uint32_t K, uint32_t& k, uint32_t& j) {
+    if (PB_FRAME_GROUP == 0u) { k = slot / n_px; j = slot - k * n_px; return; }
+    const uint32_t G = PB_FRAME_GROUP, full = n_px / G, body = full * G * K;
+    if (slot < body) { const uint32_t g = slot / (G * K), rem = slot - g * G * K; k = rem / G; j = g * G + (rem - k * G); return; }
+    const uint32_t r = n_px - full * G, rem = slot - body;
+    k = rem / r; j = full * G + (rem - k * r);
+}
+__device__ __forceinline__ uint32_t kj_to_slot(uint32_t k, uint32_t j, uint32_t n_px, uint32_t K) {
+    if (PB_FRAME_GROUP == 0u) return k * n_px + j;
+    const uint32_t G = PB_FRAME_GROUP, full = n_px / G, g = j / G;
+    if (g < full) return g * G * K + k * G + (j - g * G);
+    return full * G * K + k * (n_px - full * G) + (j - full * G);
+}
+
 // ---- generate: camera rays of K frames (main.cu:37-75) ----------------------------------------------
 __global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_t n_paths) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= n_paths) return;
-    const uint32_t k = slot / sc.n_px, pixel = path_pixel(slot - k * sc.n_px, sc.width, sc.height);
+    uint32_t k, j;
+    slot_to_kj(slot, sc.n_px, sc.kw, k, j);
+    const uint32_t pixel = path_pixel(j, sc.width, sc.height);
     const uint32_t x = pixel % sc.width, y = pixel / sc.width;
     Rng rng;
     rng.init(pixel, s.cnt[C_FRAME0] + k * sc.stride);
@@ -307,9 +331,10 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
             int depth = (int)(fl & F_DEPTH_MASK);
             if (depth == 0) {  // primary hit: main.cu:87-101
                 if (emitter_index >= 0) radiance += emitter_radiance(sc.em.rec[emitter_index], geo.texcoord);
-                const uint32_t k = slot / sc.n_px;
+                uint32_t k, j;
+                slot_to_kj(slot, sc.n_px, sc.kw, k, j);
                 if (k == k_aov) {
-                    const uint32_t pixel = path_pixel(slot - k * sc.n_px, sc.width, sc.height);
+                    const uint32_t pixel = path_pixel(j, sc.width, sc.height);
                     if (albedo) { const V3 a = bsdf_albedo<MAT>(bsdf); albedo[3 * pixel] = a.x; albedo[3 * pixel + 1] = a.y; albedo[3 * pixel + 2] = a.z; }
                     if (normal) { normal[3 * pixel] = geo.normal.x; normal[3 * pixel + 1] = geo.normal.y; normal[3 * pixel + 2] = geo.normal.z; }
                 }
@@ -398,9 +423,10 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
         const uint32_t fl = __float_as_uint(ro4.w);
         const bool primary = (fl & F_DEPTH_MASK) == 0u;
         if (primary) {
-            const uint32_t k = slot / sc.n_px;
+            uint32_t k, j;
+            slot_to_kj(slot, sc.n_px, sc.kw, k, j);
             if (k == k_aov) {
-                const uint32_t pixel = path_pixel(slot - k * sc.n_px, sc.width, sc.height);
+                const uint32_t pixel = path_pixel(j, sc.width, sc.height);
                 if (albedo) { albedo[3 * pixel] = 0.f; albedo[3 * pixel + 1] = 0.f; albedo[3 * pixel + 2] = 0.f; }
                 if (normal) { normal[3 * pixel] = 0.f; normal[3 * pixel + 1] = 0.f; normal[3 * pixel + 2] = 0.f; }
             }
@@ -428,7 +454,7 @@ __global__ void __launch_bounds__(256) k_accumulate(WfState s, float4* sum, uint
     const uint32_t pixel = path_pixel(j, width, height);
     float4 a = sum[pixel];
     for (uint32_t k = 0; k < k_count; ++k) {
-        const float4 r = s.rec[(size_t)R_COUNT * ((size_t)k * n_px + j) + R_RAD];
+        const float4 r = s.rec[(size_t)R_COUNT * kj_to_slot(k, j, n_px, k_count) + R_RAD];
         a.x += r.x; a.y += r.y; a.z += r.z; a.w += 1.f;
     }
     sum[pixel] = a;
@@ -576,6 +602,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     for (uint32_t k0 = 0; k0 < p->sample_count; k0 += K) {
         const uint32_t kw = std::min(K, p->sample_count - k0);
         const uint32_t n_paths = kw * n_px;
+        sc.kw = kw;
         const bool last_wave = k0 + kw >= p->sample_count;
         const uint32_t k_aov = last_wave ? kw - 1 : 0xFFFFFFFFu;   // AOVs of the last frame (main.cu:94-99)
         k_set_frame0<<<1, 1, 0, s>>>(st, p->first_sample + k0 * sc.stride);
