@@ -39,6 +39,8 @@ def render_pair(api, oracle_api, variant, w, h, depth, spp, first=0, stride=1):
 @pytest.mark.parametrize("variant,w,h,depth,spp", [("diffuse", 256, 256, 8, 1), ("diffuse", 256, 256, 8, 16),
                                                    ("materials", 192, 192, 8, 1), ("materials", 192, 192, 8, 16),
                                                    ("materials", 64, 48, 1, 2), ("materials", 64, 48, 2, 2),
+                                                   ("materials", 37, 23, 4, 3),   # odd film: short last strip / last frame group
+
                                                    ("textured", 160, 160, 8, 4), ("envmap", 160, 160, 8, 4)])
 def test_cornell_matches_oracle(api, oracle_api, variant, w, h, depth, spp):
     o, g, (so, ao, no), (sg, ag, ng) = render_pair(api, oracle_api, variant, w, h, depth, spp)
