@@ -58,6 +58,7 @@ def main():
     ap.add_argument("--mesh", default="10M", help="1M | 10M | 100M, or a comma list (primary rays are generated once)")
     ap.add_argument("--rays", type=int, default=20_000_000, help="primary rays (C3: 100000000)")
     ap.add_argument("--incoherent", type=int, default=0, help="size of the incoherent set (0 = one bounce ray per primary hit; C3: 100000000)")
+    ap.add_argument("--orders", action="store_true", help="also time the incoherent set in primary-pixel order and binned by direction octant")
     ap.add_argument("--no-sorted", action="store_true", help="skip the origin-Morton-sorted variant of the incoherent set")
     ap.add_argument("--spheres", type=int, default=0)
     ap.add_argument("--check", type=int, default=0)
@@ -117,6 +118,11 @@ def one_mesh(args, mesh_name, prim, api, capi, scenes, torch, dev, stream, peak)
 
     hp = run("coherent primary", prim)
     inc = bounce_rays(prim, hp, target=args.incoherent)
+    if args.orders:   # diagnostic: the same rays in the order a wavefront would hold them, and binned by direction octant
+        run("incoherent bounce (primary-pixel order)", inc)
+        octant = (inc["dx"] < 0).astype(np.int8) * 4 + (inc["dy"] < 0).astype(np.int8) * 2 + (inc["dz"] < 0).astype(np.int8)
+        run("incoherent bounce (primary-pixel order, binned by direction octant)", inc[np.argsort(octant, kind="stable")])
+        del octant
     rng = np.random.RandomState(5)
     inc = inc[rng.permutation(len(inc))]            # queue order of a wavefront after compaction: unordered
     hi = run("incoherent bounce (unordered)", inc)
