@@ -56,17 +56,28 @@ def peaks():
 
 
 class ClockSampler:
-    """SM clock, power and throttle reasons sampled every 100 ms DURING the timed region.  NVML is opened (and
-    its first, slow queries made) before the warm-up steps so that no driver initialisation lands inside the
-    timed region; only samples taken between begin() and end() are reported.  In-process NVML (nvidia-ml-py),
-    falling back to a streaming `nvidia-smi -lms` child started at construction."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+    """SM clock, power and throttle reasons sampled every 100 ms DURING the timed region, OUT OF PROCESS: a streaming
+    `nvidia-smi -lms 100` child started well before the warm-up writes timestamped rows into a pipe that nobody reads
+    until the timed region is over (10 rows / s against a 64 KB pipe buffer), so the sampler never competes with the
+    enqueuing thread for the GIL (an in-process NVML poller delayed the first enqueue of a timed region by up to 20 ms:
+    every hand-over of the GIL can cost a 5 ms switch interval).  Rows are selected by their wall-clock time stamp
+    between begin() and end().  In-process NVML (nvidia-ml-py) is only the fallback when nvidia-smi is missing."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int, uuid=None):
         self.rows, self.proc, self.h, self.nv = [], None, None, None
         self.t0 = self.t1 = None
         self.alive = True
+        self.wall = False      # rows carry wall-clock stamps (nvidia-smi) instead of perf_counter stamps (NVML thread)
+        try:
+            sel = ("GPU-" + str(uuid)) if uuid else str(index)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", sel], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.wall = True
+            return
+        except Exception:
+            self.proc = None
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -76,16 +87,8 @@ class ClockSampler:
             self.rows.clear()
             self.t = threading.Thread(target=self._poll, daemon=True)
             self.t.start()
-            return
         except Exception:
             self.h = None
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
-                                          "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except Exception:
-            self.proc = None
 
     def _sample(self):
         nv, h = self.nv, self.h
@@ -104,28 +107,31 @@ class ClockSampler:
                 pass
             time.sleep(0.1)
 
-    def _read(self):
+    def _drain(self):
+        """Parse everything the nvidia-smi child has written (called once, after it was terminated)."""
+        import datetime
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.proc.stdout:
+        try:
+            out = self.proc.stdout.read()
+        except Exception:
+            out = ""
+        for line in out.splitlines():
             r = [x.strip() for x in line.split(",")]
             try:
-                self.rows.append((time.perf_counter(), float(r[0]), float(r[1]), float(r[2]),
-                                  [n for n, v in zip(names, r[3:7]) if v.lower().startswith("active")]))
+                ts = datetime.datetime.strptime(r[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                self.rows.append((ts, float(r[1]), float(r[2]), float(r[3]),
+                                  [n for n, v in zip(names, r[4:8]) if v.lower().startswith("active")]))
             except Exception:
                 continue
 
+    def _now(self):
+        return time.time() if self.wall else time.perf_counter()
+
     def begin(self):
-        self.t0 = time.perf_counter()
+        self.t0 = self._now()
 
     def end(self):
-        self.t1 = time.perf_counter()
-
-    def window(self) -> dict:
-        """Summary of the samples between the last begin() and end(); sampling goes on."""
-        if self.h is None and not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml / nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        return self._summary()
+        self.t1 = self._now()
 
     def stop(self) -> dict:
         if self.h is None and not self.proc:
@@ -134,6 +140,7 @@ class ClockSampler:
         self.alive = False
         if self.proc:
             self.proc.terminate()
+            self._drain()
             try:
                 self.proc.wait(timeout=5)
             except Exception:
@@ -148,7 +155,7 @@ class ClockSampler:
         reasons = sorted({n for r in rows for n in r[4]})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_min_mhz": min(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons,
-                "source": "nvml" if self.h is not None else "nvidia-smi"}
+                "source": "nvidia-smi -lms 100 (child process)" if self.proc else "nvml (in-process thread)"}
 
 
 def build_scene(ctx, mesh_tag: str, mesh=None):
@@ -235,6 +242,13 @@ def product_main(args):
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N = world
+    clocks = None
+    if rank == 0:   # started before the scene is built: the child is sampling long before the timed region begins
+        try:
+            uuid = torch.cuda.get_device_properties(local).uuid
+        except Exception:
+            uuid = None
+        clocks = ClockSampler(local, uuid)
     api = capi.load()
     g = capi.Context(api, local)
     info, mesh = build_scene(g, args.mesh)
@@ -269,13 +283,6 @@ def product_main(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    clocks = None
-    if rank == 0:
-        try:
-            uuid = torch.cuda.get_device_properties(dev).uuid
-        except Exception:
-            uuid = None
-        clocks = ClockSampler(local, uuid)
     for i in range(args.warmup):
         dev_step(i)
     barrier()
@@ -291,18 +298,23 @@ def product_main(args):
     # the K steps are enqueued back to back on the stream (PB_RENDER_ASYNC; the film of step i is consumed by the
     # reduce / add enqueued right behind it) and synchronised once: the timed region holds device work only,
     # a host hiccup between two steps cannot idle the GPU
+    marks, host_ms = [], []
     for i in range(args.steps):
+        t_i = time.perf_counter()
         dev_step(args.warmup + i, asynchronous=True)
+        host_ms.append(round((time.perf_counter() - t_i) * 1e3, 2))
+        ev = torch.cuda.Event(enable_timing=True); ev.record(stream); marks.append(ev)
     e1.record(stream)
     barrier()
     if clocks:
         clocks.end()
     ms = e0.elapsed_time(e1)
+    gpu_step_ms = [round((e0 if i == 0 else marks[i - 1]).elapsed_time(marks[i]), 2) for i in range(len(marks))]   # device timeline, step by step
     st = g.stats()            # totals of the K asynchronous renders
     rays_c, rays_a, launches = st["rays_closest"], st["rays_any"], st["kernel_launches"] + (args.steps if rank == 0 else 0)
     ext_ms, con_ms, shd_ms, ext_l, con_l = st["extend_ms"], st["connect_ms"], st["shade_ms"], st["extend_launches"], st["connect_launches"]
     step_ms = [round(st["last_render_ms"] / args.steps, 2)]
-    clk = clocks.stop() if clocks else None   # in-process NVML polling delays the per-step enqueue of the e2e loop (measured: +70 ms spikes): off from here
+    clk = clocks.stop() if clocks else None
     t = torch.tensor([ms, float(rays_c), float(rays_a), float(launches)], dtype=torch.float64, device=dev)
     if N > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -355,7 +367,7 @@ def product_main(args):
     # reported: the same steps as synchronous calls, one at a time ("sync": exposed to host scheduling noise between
     # calls - on shared boxes single steps took up to +50 ms).
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    e2e_ms, _ = e2e_run(True)
+    e2e_ms, e2e_async_host = e2e_run(True)
     sync_ms, e2e_each = e2e_run(False)
     e2e_value = float(n_px) * S * e2e_steps * N / (e2e_ms * 1e-3) / 1e6
     sync_value = float(n_px) * S * e2e_steps * N / (sync_ms * 1e-3) / 1e6
@@ -395,6 +407,8 @@ def product_main(args):
                                      "avg_launch_ms": con_ms / max(1, con_l), "launches": con_l,
                                      "share_of_step": con_ms / ms if N == 1 else None}
         extra["render_ms_each_step"] = step_ms
+        extra["gpu_ms_each_step"] = gpu_step_ms
+        extra["host_enqueue_ms_each_step"] = host_ms
         extra["shade_share_of_step"] = shd_ms / ms if N == 1 else None
         extra["mrays_per_s_closest_kernel"] = rays_c / (ext_ms * 1e-3) / 1e6 if ext_ms > 0 else None
         extra["mrays_per_s_any_kernel"] = rays_a / (con_ms * 1e-3) / 1e6 if con_ms > 0 else None
@@ -416,7 +430,7 @@ def product_main(args):
                            "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"},
                 "mrays_per_s": mrays, "rays_per_sample": (rays_c_all + rays_a_all) / samples,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "api": "pb_render(PB_RENDER_HOST_BUFFERS | PB_RENDER_ASYNC) x steps + pb_wait",
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "api": "pb_render(PB_RENDER_HOST_BUFFERS | PB_RENDER_ASYNC) x steps + pb_wait", "host_enqueue_ms_each": e2e_async_host,
                         "sync": {"value": sync_value, "ms_per_step": sync_ms / e2e_steps, "ms_each": e2e_each, "api": "pb_render(PB_RENDER_HOST_BUFFERS), one synchronous call per step"}},
                 "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
                 "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}

@@ -44,6 +44,8 @@ struct pb_ctx {
     float* d_pos = nullptr; float* d_nrm = nullptr; float* d_uv = nullptr; uint32_t* d_idx = nullptr;
     uint64_t scene_epoch = 1;            // bumped by commit / set_camera: captured wave graphs of older epochs are dropped
     bool use_graphs = true;              // PB_NO_GRAPH=1 launches kernel by kernel
+    bool wave_target_env = false;        // wave_target came from PB_WAVE_PATHS
+    uint32_t wave_target = 0;            // paths per wave, decided once per context (cudaMemGetInfo is too slow for every pb_render)
     float* d_stage = nullptr;            // film staging of the host-buffer pb_render path (sum 16 B + albedo 12 B + normal 12 B per pixel), grow-only
     size_t stage_px = 0;
     float* d_trishade = nullptr;         // 24 floats per triangle (pb_scene.cuh)

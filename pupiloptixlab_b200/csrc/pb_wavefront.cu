@@ -559,7 +559,11 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     if ((uint64_t)p->width * p->height > (1ull << 30)) { c->err = "film too large"; return PB_ERR_LIMIT; }
     if (p->flags & PB_RENDER_CLEAR) PB_CUDA_TRY(c, cudaMemsetAsync(d_sum, 0, (size_t)n_px * 16, s));
     if (p->sample_count == 0) return PB_OK;
-    uint32_t K = std::max<uint32_t>(1u, wave_path_target() / n_px);
+    // decided on the first render of a context with the state already allocated by its scene, and kept (PB_WAVE_PATHS is
+    // still read every time: tests change it): cudaMemGetInfo took up to 95 ms at the head of a pb_render on a busy box
+    { const bool env = getenv("PB_WAVE_PATHS") != nullptr;
+      if (c->wave_target == 0u || env || c->wave_target_env) { c->wave_target = wave_path_target(); c->wave_target_env = env; } }
+    uint32_t K = std::max<uint32_t>(1u, c->wave_target / n_px);
     K = std::min(K, p->sample_count);
     if ((uint64_t)K * n_px > 0x7fffffffull) { c->err = "wave too large"; return PB_ERR_LIMIT; }
     int rc = wavefront_reserve(c, K * n_px);
