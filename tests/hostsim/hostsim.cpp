@@ -12,6 +12,7 @@
 #include "../../pupiloptixlab_b200/csrc/pb_collapse.cuh"
 #include "../../pupiloptixlab_b200/csrc/pb_host_math.h"
 #include "../../pupiloptixlab_b200/csrc/pb_scene.cuh"
+#include "../../pupiloptixlab_b200/csrc/pb_slots.cuh"
 
 using namespace pb;
 
@@ -150,5 +151,17 @@ void hs_trace_any(HS* h, const float* rays, uint64_t n, uint8_t* occ) {
         traverse<true, true>(sc, {r[0], r[1], r[2]}, {r[4], r[5], r[6]}, r[3], r[7], hit, st, &h->cnt);
         occ[i] = hit.prim != 0xFFFFFFFFu;
     }
+}
+// wave slot -> (frame, pixel) for every slot of a wave of K frames of a w x h film, and the inverse used by k_accumulate
+void hs_slot_tables(uint32_t w, uint32_t h, uint32_t K, uint32_t* frame_of_slot, uint32_t* pixel_of_slot, uint32_t* slot_of_kj) {
+    const uint32_t n_px = w * h;
+    for (uint32_t slot = 0; slot < K * n_px; ++slot) {
+        uint32_t k, j;
+        slot_to_kj(slot, n_px, K, k, j);
+        frame_of_slot[slot] = k;
+        pixel_of_slot[slot] = j < n_px ? path_pixel(j, w, h) : 0xFFFFFFFFu;
+    }
+    for (uint32_t k = 0; k < K; ++k)
+        for (uint32_t j = 0; j < n_px; ++j) slot_of_kj[(size_t)k * n_px + j] = kj_to_slot(k, j, n_px, K);
 }
 }  // extern "C"
