@@ -102,7 +102,9 @@ typedef struct pb_hit { float t, u, v; uint32_t prim; } pb_hit;               /*
 /* ---- render parameters: Pupil::pt::OptixLaunchParams::config + seeds (path_tracer/type.h:9-33) */
 typedef struct pb_render_params {
     uint32_t width, height;
-    uint32_t max_depth;     /* config.max_depth                                                  */
+    uint32_t max_depth;     /* config.max_depth, read as the reference's int (type.h:12): a path scatters at
+                               most max_depth - 1 times after the primary hit (main.cu:104-106), so values
+                               <= 1 (mitsuba's -1 included) render the primary hit only; > 1024: PB_ERR_LIMIT */
     uint32_t first_sample;  /* random_seed of the first frame rendered by this call              */
     uint32_t sample_count;  /* number of frames (1 frame = 1 spp, pt_pass.cpp:51-56)             */
     uint32_t sample_stride; /* frame index step (multi-GPU sample interleave); 0 means 1         */
@@ -192,6 +194,16 @@ PB_API int pb_trace_any_counted(pb_ctx* ctx, const pb_ray* rays, uint64_t n, uin
  * floats of the last frame (main.cu:94-99) or NULL.                                              */
 PB_API int pb_render(pb_ctx* ctx, const pb_render_params* p, float* accum_sum_rgba, float* albedo_rgb,
                      float* normal_rgb, void* cuda_stream);
+/* pb_render with every output buffer of the pass contract (pt_pass.cpp:123-147): "pt accum buffer", "albedo",
+ * "normal" and "test" (main.cu:101: the RNG draw that follows the primary hit, one float per pixel, last frame).
+ * accum_sum_rgba is required, the others may be NULL.  Device pointers unless PB_RENDER_HOST_BUFFERS.          */
+typedef struct pb_render_targets {
+    float* accum_sum_rgba;   /* w*h float4 */
+    float* albedo_rgb;       /* w*h*3      */
+    float* normal_rgb;       /* w*h*3      */
+    float* test;             /* w*h        */
+} pb_render_targets;
+PB_API int pb_render_ex(pb_ctx* ctx, const pb_render_params* p, const pb_render_targets* targets, void* cuda_stream);
 /* "frame buffer" of the reference: mean = sum.xyz / sum.w, alpha 1 (main.cu:192-193)             */
 PB_API int pb_resolve(pb_ctx* ctx, const float* accum_sum_rgba, float* frame_rgba, uint32_t n_pixels,
                       int host, void* cuda_stream);

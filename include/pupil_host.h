@@ -67,6 +67,24 @@ PH_API const ph_sink* ph_default_sink(void);
 PH_API int  ph_run_path_tracer(const char* xml_path, int device, uint32_t frames, float* final_rgba,
                                float* albedo_rgb, float* normal_rgb, uint32_t* out_w, uint32_t* out_h);
 
+/* The same loop as an object, for callers that interleave rendering with scene edits (the reference's GUI thread does
+ * this through the event system): System + one B200PTPass kept alive between calls.
+ *   ph_session_run          n more frames (System::Run's loop body, system.cpp:96-101)
+ *   ph_session_move_object  RenderObject::UpdateTransform (render_object.cpp:46-49) of shape instance `index`: raises
+ *                           EWorldEvent::RenderInstanceTransform -> World updates the instance -> RenderInstanceUpdate ->
+ *                           the pass restarts accumulation against the moved geometry (pt_pass.cpp:40-49,216-218)
+ *   ph_session_read         copy a named BufferManager buffer ("final result", "pt accum buffer", "albedo", "normal",
+ *                           "test") to host memory; bytes must equal the buffer size
+ *   ph_session_sample_count frames accumulated since the last restart (sample_cnt, pt_pass.cpp:43,55)           */
+typedef struct ph_session ph_session;
+PH_API int  ph_session_create(const char* xml_path, int device, ph_session** out);
+PH_API void ph_session_destroy(ph_session* s);
+PH_API int  ph_session_run(ph_session* s, uint32_t frames);
+PH_API int  ph_session_move_object(ph_session* s, uint32_t index, const float to_world[16]);
+PH_API int  ph_session_read(ph_session* s, const char* buffer_name, void* dst, uint64_t bytes);
+PH_API int  ph_session_film(const ph_session* s, uint32_t* w, uint32_t* h);
+PH_API uint32_t ph_session_sample_count(const ph_session* s);
+
 /* util::BitmapTexture::Load / Save (framework/util/texture.cpp:87-180).  Load: PNG / BMP / TGA / PPM through the
  * reference's pow(x/255, 2.2) decode, Radiance .hdr / OpenEXR (scanline; none / zips / zip) / PFM as float data;
  * returns RGBA float texels (row 0 = top) in a buffer released by ph_image_free.  Save: by extension .hdr / .exr

@@ -573,7 +573,7 @@ static const EmitterRec& select_emitter(const Ctx* c, float p) {
 
 template<class B>
 static f3 path_radiance(const Ctx* c, const pb_render_params& rp, uint32_t x, uint32_t y, uint32_t seed,
-                        f3& albedo, f3& normal, Counters& cnt) {
+                        f3& albedo, f3& normal, float& test, Counters& cnt) {
     const uint32_t w = rp.width, h = rp.height;
     const uint32_t pixel_index = y * w + x;
     Rng rng;
@@ -623,11 +623,14 @@ static f3 path_radiance(const Ctx* c, const pb_render_params& rp, uint32_t x, ui
         albedo = mk3(0.f);
         normal = mk3(0.f);
     }
-    (void)B::rng_next(rng);  // test[pixel] = rng.Next(), main.cu:101
+    test = B::rng_next(rng);  // test[pixel] = rng.Next(), main.cu:101
+    // A scene without any emitter: the reference dereferences a null emitter group in the NEE block
+    // (emitter.h:110-136); normalised on both sides to "the path ends at the primary vertex" (radiance 0 either way).
+    const bool no_emitters = c->areas.empty() && c->env.type == kEmNone;
 
     while (!done) {
         ++depth;
-        if (depth >= (int)rp.max_depth) break;
+        if (depth >= (int)rp.max_depth || no_emitters) break;
         float rr = depth > 2 ? 0.95 : 1.0;
         if (B::rng_next(rng) > rr) break;
         throughput /= rr;
@@ -690,10 +693,15 @@ static f3 path_radiance(const Ctx* c, const pb_render_params& rp, uint32_t x, ui
     return radiance;
 }
 
+// Window [x0, x0+ww) x [y0, y0+wh) of the film (the whole film by default): output buffers are window-sized,
+// seeds stay those of the full film (pixel_index = y * width + x), so a crop of a large film costs only its pixels.
+struct Window { uint32_t x0, y0, w, h; };
 template<class B>
-static int render(Ctx* c, const pb_render_params* rp, float* sum, float* albedo, float* normal) {
-    uint32_t w = rp->width, h = rp->height;
-    size_t npx = (size_t)w * h;
+static int render(Ctx* c, const pb_render_params* rp, float* sum, float* albedo, float* normal, float* test = nullptr,
+                  const Window* win = nullptr) {
+    const Window full{0u, 0u, rp->width, rp->height};
+    const Window W = win ? *win : full;
+    size_t npx = (size_t)W.w * W.h;
     if (rp->flags & PB_RENDER_CLEAR) memset(sum, 0, npx * 16);
     uint32_t stride = rp->sample_stride ? rp->sample_stride : 1;
     auto t0 = std::chrono::steady_clock::now();
@@ -701,15 +709,17 @@ static int render(Ctx* c, const pb_render_params* rp, float* sum, float* albedo,
     for (uint32_t s = 0; s < rp->sample_count; ++s) {
         uint32_t seed = rp->first_sample + s * stride;
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : rc, ra)
-        for (int y = 0; y < (int)h; ++y) {
+        for (int yy = 0; yy < (int)W.h; ++yy) {
             Counters cnt;
-            for (uint32_t x = 0; x < w; ++x) {
+            for (uint32_t xx = 0; xx < W.w; ++xx) {
                 f3 a, n;
-                f3 L = path_radiance<B>(c, *rp, x, (uint32_t)y, seed, a, n, cnt);
-                size_t p = (size_t)y * w + x;
+                float tv = 0.f;
+                f3 L = path_radiance<B>(c, *rp, W.x0 + xx, W.y0 + (uint32_t)yy, seed, a, n, tv, cnt);
+                size_t p = (size_t)yy * W.w + xx;
                 sum[4 * p + 0] += L.x; sum[4 * p + 1] += L.y; sum[4 * p + 2] += L.z; sum[4 * p + 3] += 1.f;
                 if (albedo) { albedo[3 * p] = a.x; albedo[3 * p + 1] = a.y; albedo[3 * p + 2] = a.z; }
                 if (normal) { normal[3 * p] = n.x; normal[3 * p + 1] = n.y; normal[3 * p + 2] = n.z; }
+                if (test) test[p] = tv;
             }
             rc += cnt.rays_closest; ra += cnt.rays_any;
         }
@@ -886,6 +896,28 @@ ORC_API int orc_render(orc_ctx* c, const pb_render_params* p, float* sum, float*
     if (c->backend == 1) return render<RefBackend>(c, p, sum, albedo, normal);
 #endif
     return render<PortBackend>(c, p, sum, albedo, normal);
+}
+// pb_render_ex of the header (adds the "test" buffer, pt_pass.cpp:144-146 / main.cu:101)
+ORC_API int orc_render_ex(orc_ctx* c, const pb_render_params* p, const pb_render_targets* t, void*) {
+    CHECK(c->committed, "scene not committed");
+    CHECK(p && t && t->accum_sum_rgba, "null render params / targets");
+    CHECK(p->width && p->height, "empty film");
+#ifdef ORC_WITH_REFERENCE
+    if (c->backend == 1) return render<RefBackend>(c, p, t->accum_sum_rgba, t->albedo_rgb, t->normal_rgb, t->test);
+#endif
+    return render<PortBackend>(c, p, t->accum_sum_rgba, t->albedo_rgb, t->normal_rgb, t->test);
+}
+// oracle only: a window of the film (window-sized output buffers, full-film seeds)
+ORC_API int orc_render_window(orc_ctx* c, const pb_render_params* p, const pb_render_targets* t, uint32_t x0, uint32_t y0,
+                              uint32_t w, uint32_t h) {
+    CHECK(c->committed, "scene not committed");
+    CHECK(p && t && t->accum_sum_rgba, "null render params / targets");
+    CHECK(w && h && x0 + w <= p->width && y0 + h <= p->height, "window outside the film");
+    const Window win{x0, y0, w, h};
+#ifdef ORC_WITH_REFERENCE
+    if (c->backend == 1) return render<RefBackend>(c, p, t->accum_sum_rgba, t->albedo_rgb, t->normal_rgb, t->test, &win);
+#endif
+    return render<PortBackend>(c, p, t->accum_sum_rgba, t->albedo_rgb, t->normal_rgb, t->test, &win);
 }
 ORC_API int orc_resolve(orc_ctx*, const float* sum, float* frame, uint32_t n, int, void*) {
     for (uint32_t i = 0; i < n; ++i) {

@@ -40,6 +40,7 @@ def _extend(api: capi.Api) -> capi.Api:
     api._f("rng_stream", i32, [vp, u32, u32, u32, C.POINTER(u32), fpp])
     api._f("bsdf_table", i32, [vp, u32, fpp, C.POINTER(u32), u32, fpp])
     api._f("emitter_table", i32, [vp, u32, fpp, fpp, fpp, u32, fpp])
+    api._f("render_window", i32, [vp, C.POINTER(capi.RenderParams), C.POINTER(capi.RenderTargets), u32, u32, u32, u32])
     api._f("trace_cwbvh", i32, [vp, vp, u64, vp, u64, vp, u64, vp, C.POINTER(u64), i32], optional=True)
     return api
 
@@ -82,6 +83,16 @@ class OracleContext(capi.Context):
         occ = np.empty(rays.shape[0], np.uint8)
         self._ck(self.api._trace_any_brute(self.h, rays.ctypes.data, rays.shape[0], occ.ctypes.data), "trace_any_brute")
         return occ
+
+    def render_window(self, width, height, max_depth, first_sample, sample_count, x0, y0, w, h, sample_stride=1):
+        """Window [x0, x0+w) x [y0, y0+h) of a width x height film (full-film seeds): (sum, albedo, normal, test), window-sized."""
+        p = capi.RenderParams(width, height, max_depth, first_sample, sample_count, sample_stride, capi.RENDER_CLEAR, 0)
+        acc = np.zeros((h, w, 4), np.float32)
+        alb, nrm = np.zeros((h, w, 3), np.float32), np.zeros((h, w, 3), np.float32)
+        tst = np.zeros((h, w), np.float32)
+        t = capi.RenderTargets(acc.ctypes.data, alb.ctypes.data, nrm.ctypes.data, tst.ctypes.data)
+        self._ck(self.api._render_window(self.h, C.byref(p), C.byref(t), x0, y0, w, h), "render_window")
+        return acc, alb, nrm, tst
 
     def rng_stream(self, v0: int, v1: int, n: int):
         seed = C.c_uint32()

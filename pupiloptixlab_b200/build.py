@@ -74,6 +74,31 @@ def build_host(force: bool = False) -> str:
     return HOST_OUT
 
 
+TESTS_DIR = os.path.join(os.path.dirname(HERE), "tests")
+
+
+def build_devsim(force: bool = False) -> str:
+    """TEST HARNESS (not product): tests/devsim/devsim.cu -> tests/devsim/libdevsim.so, the product's shading headers
+    on the GPU outside the integrator, same nvcc flags as the product (-fmad=false).  Built here because the .so
+    travels to the GPU box with the snapshot."""
+    d = os.path.join(TESTS_DIR, "devsim")
+    out = os.path.join(d, "libdevsim.so")
+    deps = [os.path.join(d, f) for f in os.listdir(d) if f.endswith((".cu", ".h"))]
+    deps += [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    if not force and _newer(out, deps):
+        return out
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    env = dict(os.environ)
+    env["PATH"] = "/usr/bin:" + env.get("PATH", "")
+    flags = [f for f in NVCC_FLAGS if f not in ("-Xptxas", "-v")]
+    cmd = [nvcc, *flags, "-ccbin", "/usr/bin/g++", "-shared", os.path.join(d, "devsim.cu"), "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    if r.returncode != 0:
+        raise RuntimeError("devsim build failed:\n" + r.stdout + r.stderr)
+    return out
+
+
 if __name__ == "__main__":
     print(build_native(force="--force" in sys.argv, verbose="-v" in sys.argv))
     print(build_host(force="--force" in sys.argv))
+    print(build_devsim(force="--force" in sys.argv))

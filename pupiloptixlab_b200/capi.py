@@ -49,6 +49,10 @@ class RenderParams(C.Structure):
                 ("flags", C.c_uint32), ("_pad", C.c_uint32)]
 
 
+class RenderTargets(C.Structure):
+    _fields_ = [("accum_sum_rgba", C.c_void_p), ("albedo_rgb", C.c_void_p), ("normal_rgb", C.c_void_p), ("test", C.c_void_p)]
+
+
 class Stats(C.Structure):
     _fields_ = [("rays_closest", C.c_uint64), ("rays_any", C.c_uint64), ("samples", C.c_uint64),
                 ("node_visits", C.c_uint64), ("prim_tests_tri", C.c_uint64), ("prim_tests_sphere", C.c_uint64),
@@ -194,6 +198,7 @@ class Api:
         f("trace_closest", i32, [vp, vp, u64, vp, i32, vp])
         f("trace_any", i32, [vp, vp, u64, vp, i32, vp])
         f("render", i32, [vp, C.POINTER(RenderParams), vp, vp, vp, vp])
+        f("render_ex", i32, [vp, C.POINTER(RenderParams), C.POINTER(RenderTargets), vp])
         f("resolve", i32, [vp, vp, vp, u32, i32, vp])
         f("get_stats", i32, [vp, C.POINTER(Stats)])
         if self.prefix == "pb_":      # the oracle is synchronous and has no display transform
@@ -321,6 +326,17 @@ class Context:
         self._ck(self.api._render(self.h, C.byref(p), acc.ctypes.data, alb.ctypes.data if want_aov else None,
                                   nrm.ctypes.data if want_aov else None, None), "render")
         return acc, alb, nrm
+
+    def render_ex(self, width, height, max_depth, first_sample, sample_count, sample_stride=1, clear=True):
+        """pb_render_ex with host buffers: returns (sum_rgba, albedo, normal, test[h,w])."""
+        p = RenderParams(width, height, max_depth, first_sample, sample_count, sample_stride,
+                         RENDER_HOST_BUFFERS | (RENDER_CLEAR if clear else 0), 0)
+        acc = np.zeros((height, width, 4), np.float32)
+        alb, nrm = np.zeros((height, width, 3), np.float32), np.zeros((height, width, 3), np.float32)
+        tst = np.zeros((height, width), np.float32)
+        t = RenderTargets(acc.ctypes.data, alb.ctypes.data, nrm.ctypes.data, tst.ctypes.data)
+        self._ck(self.api._render_ex(self.h, C.byref(p), C.byref(t), None), "render_ex")
+        return acc, alb, nrm, tst
 
     def render_dev(self, params: RenderParams, sum_ptr: int, albedo_ptr: int = 0, normal_ptr: int = 0, stream: int = 0):
         self._ck(self.api._render(self.h, C.byref(params), sum_ptr, albedo_ptr or None, normal_ptr or None, stream), "render")

@@ -34,6 +34,10 @@ static const float* device_texels(void* user, const pb_texture& t) {
 static int commit(pb_ctx* c) {
     cudaSetDevice(c->device);
     wavefront_wait(c);          // asynchronous renders may still read the old scene
+    // not committed until every table below exists: a failure half way (out of memory, bad environment map, BVH
+    // limit) must leave the context refusing pb_render / pb_trace_* instead of launching on freed pointers
+    c->committed = false;
+    ++c->scene_epoch;           // graphs captured against the old scene hold its device pointers
     pb_free_device_scene(c);
     c->stats = pb_stats{};
     auto t0 = std::chrono::steady_clock::now();
@@ -187,9 +191,13 @@ static int commit(pb_ctx* c) {
     for (auto& e : emit) area_weight_sum += e.weight;
     if (!emit.empty())
         for (auto& e : emit) e.select_probability = e.weight / area_weight_sum * emit.size();
+    // a scene without any emitter is legal here (the reference would dereference an empty group): no NEE, paths end at
+    // the primary vertex (pb_wavefront.cu has_emitters)
     const size_t emitter_num = (c->has_env ? 1 : 0) + emit.size();
-    for (auto& e : emit) e.select_probability = e.select_probability / emitter_num;
-    env.select_probability = env.weight / emitter_num;
+    if (emitter_num) {
+        for (auto& e : emit) e.select_probability = e.select_probability / emitter_num;
+        env.select_probability = env.weight / emitter_num;
+    }
     std::vector<float> prefix(emit.size());
     float sum_p = 0.f;
     for (size_t i = 0; i < emit.size(); ++i) { prefix[i] = sum_p + emit[i].select_probability; sum_p += emit[i].select_probability; }

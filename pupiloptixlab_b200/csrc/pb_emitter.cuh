@@ -21,7 +21,8 @@ PB_HD uint32_t select_emitter(const EmitterTable& t, float p) {
         if (p <= t.prefix[mid]) hi = mid; else lo = mid + 1;
     }
     if (lo < t.n_area) return lo;
-    return t.rec[t.n_area].type != EM_NONE ? t.n_area : t.n_area - 1;
+    // never called on an emitter-less scene (k_shade's has_emitters); the slot n_area always exists, so index it then
+    return (t.rec[t.n_area].type != EM_NONE || t.n_area == 0u) ? t.n_area : t.n_area - 1;
 }
 
 struct EmitterSample { V3 radiance, wi; float distance, pdf; bool valid_distance; };

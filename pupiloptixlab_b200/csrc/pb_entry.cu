@@ -82,35 +82,42 @@ PB_API int pb_trace_any_counted(pb_ctx* c, const pb_ray* rays, uint64_t n, uint8
     return trace_entry(c, rays, n, occ, host, stream, true, true);
 }
 
-PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba, float* albedo_rgb, float* normal_rgb, void* stream) {
+PB_API int pb_render_ex(pb_ctx* c, const pb_render_params* p, const pb_render_targets* tg, void* stream) {
     if (!c) return PB_ERR_INVALID;
     if (!c->committed) { c->err = "scene not committed"; return PB_ERR_NOT_COMMITTED; }
-    PB_REQUIRE(p && accum_sum_rgba, "null render params / accumulation buffer");
+    PB_REQUIRE(p && tg && tg->accum_sum_rgba, "null render params / accumulation buffer");
     PB_REQUIRE(p->width && p->height, "empty film");
+    float* accum_sum_rgba = tg->accum_sum_rgba;
+    float* albedo_rgb = tg->albedo_rgb;
+    float* normal_rgb = tg->normal_rgb;
+    float* test = tg->test;
     cudaSetDevice(c->device);
     cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
     const size_t npx = (size_t)p->width * p->height;
     if (!(p->flags & PB_RENDER_HOST_BUFFERS)) {
-        return wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, s);   // synchronises unless PB_RENDER_ASYNC
+        return wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, test, s);   // synchronises unless PB_RENDER_ASYNC
     }
     const auto h0 = std::chrono::steady_clock::now();
     // film staging lives in the context (no cudaMalloc / cudaFree - both synchronise the device - per call)
     if (c->stage_px < npx) {
+        wavefront_wait(c);   // an asynchronous render may still be writing the old staging film
         cudaFree(c->d_stage); c->d_stage = nullptr; c->stage_px = 0;
-        PB_CUDA_TRY(c, cudaMalloc(&c->d_stage, npx * 40));
+        PB_CUDA_TRY(c, cudaMalloc(&c->d_stage, npx * 44));
         c->stage_px = npx;
     }
     float* d_sum = c->d_stage;
     float* d_alb = albedo_rgb ? c->d_stage + npx * 4 : nullptr;
     float* d_nrm = normal_rgb ? c->d_stage + npx * 7 : nullptr;
+    float* d_tst = test ? c->d_stage + npx * 10 : nullptr;
     if (!(p->flags & PB_RENDER_CLEAR)) PB_CUDA_TRY(c, cudaMemcpyAsync(d_sum, accum_sum_rgba, npx * 16, cudaMemcpyHostToDevice, s));
     pb_render_params q = *p;
     q.flags |= PB_RENDER_ASYNC;          // one synchronise for kernels and copies together (wavefront_wait below)
-    int rc = wavefront_render(c, &q, d_sum, d_alb, d_nrm, s);
+    int rc = wavefront_render(c, &q, d_sum, d_alb, d_nrm, d_tst, s);
     if (rc == PB_OK) {
         cudaError_t e = cudaMemcpyAsync(accum_sum_rgba, d_sum, npx * 16, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && albedo_rgb) e = cudaMemcpyAsync(albedo_rgb, d_alb, npx * 12, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && normal_rgb) e = cudaMemcpyAsync(normal_rgb, d_nrm, npx * 12, cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess && test) e = cudaMemcpyAsync(test, d_tst, npx * 4, cudaMemcpyDeviceToHost, s);
         if (e != cudaSuccess) { c->err = std::string("render (host buffers): ") + cudaGetErrorString(e); rc = PB_ERR_CUDA; }
         const auto h1 = std::chrono::steady_clock::now();
         // PB_RENDER_ASYNC with host buffers: upload, kernels and download are all stream-ordered, so consecutive calls
@@ -125,6 +132,11 @@ PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba
         }
     }
     return rc;
+}
+
+PB_API int pb_render(pb_ctx* c, const pb_render_params* p, float* accum_sum_rgba, float* albedo_rgb, float* normal_rgb, void* stream) {
+    const pb_render_targets tg{accum_sum_rgba, albedo_rgb, normal_rgb, nullptr};
+    return pb_render_ex(c, p, &tg, stream);
 }
 
 PB_API int pb_resolve(pb_ctx* c, const float* sum, float* frame, uint32_t n, int host, void* stream) {

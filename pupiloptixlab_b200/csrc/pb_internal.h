@@ -98,7 +98,7 @@ int make_world_prims(pb_ctx* c, PrimRec* d_out, cudaStream_t s);   // also compu
 // pb_trace.cu
 int trace_rays(pb_ctx* c, const pb_ray* d_rays, uint64_t n, pb_hit* d_hits, uint8_t* d_occ, bool any, bool counted, cudaStream_t s);
 // pb_wavefront.cu
-int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, cudaStream_t s);
+int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, float* d_test, cudaStream_t s);
 void wavefront_free(pb_ctx* c);
 int tonemap_frame(pb_ctx* c, const float* d_frame, uint8_t* d_rgba8, uint32_t n, int tone, int gamma, cudaStream_t s);
 int wavefront_wait(pb_ctx* c);   // synchronises pending (PB_RENDER_ASYNC) renders and folds them into pb_stats

@@ -29,7 +29,8 @@ constexpr int kWfThreads = 128;
 #define PB_TRACE_MIN_BLOCKS 8   // 64 registers per thread
 #endif
 enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_FRAME0 = 13, C_COUNT = 16 };
-enum : uint32_t { F_DEPTH_MASK = 0xffu, F_DELTA = 0x100u };
+enum : uint32_t { F_DEPTH_MASK = 0xffffu, F_DELTA = 0x80000000u };   // depth <= kMaxDepthLimit fits 16 bits
+constexpr uint32_t kMaxDepthLimit = 1024u;
 constexpr float kRayTmin = 0.001f, kRayTmax = 1e16f;
 // Queue entries are visited in (increasingly random) queue order, so the first touch of a path record is a
 // DRAM round trip that nothing in the warp can overlap.  Every consumer therefore asks L2 for the records
@@ -76,6 +77,9 @@ struct WfState {
     uint32_t cap;
 };
 
+// AOV targets of the last frame (main.cu:94-101); any of them may be null
+struct AovOut { float* albedo; float* normal; float* test; };
+
 struct Wavefront {
     WfState st{};
     uint32_t cap = 0;
@@ -95,7 +99,7 @@ struct Wavefront {
     // exposed to (measured on a shared box: the enqueue of one step took 0.8 ms normally and 15-57 ms in bursts).
     struct WaveGraph {
         uint64_t epoch; uint32_t width, height, max_depth, stride, kw, k_aov;
-        float *d_sum, *d_albedo, *d_normal;
+        float *d_sum, *d_albedo, *d_normal, *d_test;
         cudaGraphExec_t exec;
     };
     std::vector<WaveGraph> graphs;
@@ -109,6 +113,7 @@ struct WfScene {
     Camera cam;
     uint32_t width, height, n_px, max_depth;
     uint32_t kw;             // frames in this wave (slot_to_kj)
+    uint32_t has_emitters;   // 0: no area emitter and no environment - paths end at the primary vertex (NEE would index an empty table)
     uint32_t stride;      // frame index step; the first frame of a wave is s.cnt[C_FRAME0] (set per wave, so that a
                           // captured wave graph can be replayed for any first_sample)
 };
@@ -258,7 +263,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfS
 
 // ---- shade<MAT>: one path vertex.  Follows main.cu:84-183 line by line -----------------------------------
 template<int MAT>
-__global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfState s, WfScene sc, int cur, uint32_t k_aov, float* albedo, float* normal) {
+__global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfState s, WfScene sc, int cur, uint32_t k_aov, AovOut aov) {
     const uint32_t n = s.cnt[C_MAT0 + MAT];
     const uint32_t* q = s.q_mat + (size_t)MAT * s.cap;
     uint32_t* qnext = cur ? s.q_ext[0] : s.q_ext[1];
@@ -295,12 +300,13 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
                 if (emitter_index >= 0) radiance += emitter_radiance(sc.em.rec[emitter_index], geo.texcoord);
                 uint32_t k, j;
                 slot_to_kj(slot, sc.n_px, sc.kw, k, j);
+                const float test_value = rng.next();  // test[pixel] = rng.Next(), main.cu:101
                 if (k == k_aov) {
                     const uint32_t pixel = path_pixel(j, sc.width, sc.height);
-                    if (albedo) { const V3 a = bsdf_albedo<MAT>(bsdf); albedo[3 * pixel] = a.x; albedo[3 * pixel + 1] = a.y; albedo[3 * pixel + 2] = a.z; }
-                    if (normal) { normal[3 * pixel] = geo.normal.x; normal[3 * pixel + 1] = geo.normal.y; normal[3 * pixel + 2] = geo.normal.z; }
+                    if (aov.albedo) { const V3 a = bsdf_albedo<MAT>(bsdf); aov.albedo[3 * pixel] = a.x; aov.albedo[3 * pixel + 1] = a.y; aov.albedo[3 * pixel + 2] = a.z; }
+                    if (aov.normal) { aov.normal[3 * pixel] = geo.normal.x; aov.normal[3 * pixel + 1] = geo.normal.y; aov.normal[3 * pixel + 2] = geo.normal.z; }
+                    if (aov.test) aov.test[pixel] = test_value;
                 }
-                (void)rng.next();  // test[pixel] = rng.Next(), main.cu:101
             } else if (emitter_index >= 0) {  // emitter hit by the BSDF sample: main.cu:171-182
                 const EmitRec& e = sc.em.rec[emitter_index];
                 EmitEval ev;
@@ -313,7 +319,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
             // ---- loop body, main.cu:103-163
             bool alive = true;
             ++depth;
-            if (depth >= (int)sc.max_depth) alive = false;
+            if (depth >= (int)sc.max_depth || !sc.has_emitters) alive = false;
             if (alive) {
                 const float rr = depth > 2 ? 0.95 : 1.0;
                 if (rng.next() > rr) alive = false;
@@ -374,7 +380,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
 }
 
 // ---- miss: __miss__default (main.cu:196-212) + main.cu:165-169,185 ----------------------------------------
-__global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_aov, float* albedo, float* normal) {
+__global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_aov, AovOut aov) {
     const uint32_t n = s.cnt[C_MAT0];
     const EmitRec& env = sc.em.rec[sc.em.n_area];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -389,8 +395,9 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
             slot_to_kj(slot, sc.n_px, sc.kw, k, j);
             if (k == k_aov) {
                 const uint32_t pixel = path_pixel(j, sc.width, sc.height);
-                if (albedo) { albedo[3 * pixel] = 0.f; albedo[3 * pixel + 1] = 0.f; albedo[3 * pixel + 2] = 0.f; }
-                if (normal) { normal[3 * pixel] = 0.f; normal[3 * pixel + 1] = 0.f; normal[3 * pixel + 2] = 0.f; }
+                if (aov.albedo) { aov.albedo[3 * pixel] = 0.f; aov.albedo[3 * pixel + 1] = 0.f; aov.albedo[3 * pixel + 2] = 0.f; }
+                if (aov.normal) { aov.normal[3 * pixel] = 0.f; aov.normal[3 * pixel + 1] = 0.f; aov.normal[3 * pixel + 2] = 0.f; }
+                if (aov.test) { Rng rng; rng.s = __float_as_uint(rec[R_RAD].w); aov.test[pixel] = rng.next(); }   // main.cu:101 runs for misses too
             }
         }
         if (env.type == EM_NONE) continue;
@@ -512,13 +519,20 @@ static int wavefront_reserve(pb_ctx* c, uint32_t cap) {
 }
 
 template<int MAT>
-static void launch_shade(const WfState& st, const WfScene& sc, int cur, uint32_t k_aov, float* alb, float* nrm, unsigned grid, cudaStream_t s) {
-    k_shade<MAT><<<grid, kWfThreads, 0, s>>>(st, sc, cur, k_aov, alb, nrm);
+static void launch_shade(const WfState& st, const WfScene& sc, int cur, uint32_t k_aov, const AovOut& aov, unsigned grid, cudaStream_t s) {
+    k_shade<MAT><<<grid, kWfThreads, 0, s>>>(st, sc, cur, k_aov, aov);
 }
 
-int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, cudaStream_t s) {
+int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, float* d_test, cudaStream_t s) {
     const uint32_t n_px = p->width * p->height;
     if ((uint64_t)p->width * p->height > (1ull << 30)) { c->err = "film too large"; return PB_ERR_LIMIT; }
+    // config.max_depth is an int in the reference (path_tracer/type.h:12; mitsuba writes -1 for "unbounded"): values <= 1
+    // end every path at its primary hit (main.cu:104-106), so one bounce is enqueued; the depth field of the path
+    // record holds 16 bits
+    const int depth_i = (int)p->max_depth;
+    if (depth_i > (int)kMaxDepthLimit) { c->err = "max_depth above 1024 is not supported"; return PB_ERR_LIMIT; }
+    const uint32_t n_bounces = depth_i <= 1 ? 1u : (uint32_t)depth_i;
+    const AovOut aov{d_albedo, d_normal, d_test};
     if (p->flags & PB_RENDER_CLEAR) PB_CUDA_TRY(c, cudaMemsetAsync(d_sum, 0, (size_t)n_px * 16, s));
     if (p->sample_count == 0) return PB_OK;
     // decided on the first render of a context with the state already allocated by its scene, and kept (PB_WAVE_PATHS is
@@ -539,9 +553,16 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     sc.cam = c->cam;
     sc.width = p->width; sc.height = p->height; sc.n_px = n_px; sc.max_depth = p->max_depth;
     sc.stride = p->sample_stride ? p->sample_stride : 1u;
+    sc.has_emitters = (c->n_area_emitters > 0u || c->has_env) ? 1u : 0u;
 
     Wavefront::Pending& pd = c->wf->pend;
     if (pd.calls && pd.stream != s) { rc = wavefront_wait(c); if (rc != PB_OK) return rc; }   // one stream at a time
+    // graphs captured against an older scene / camera: drop them (after the renders that may still be replaying them)
+    if (!c->wf->graphs.empty() && c->wf->graphs.front().epoch != c->scene_epoch) {
+        if (pd.calls) { rc = wavefront_wait(c); if (rc != PB_OK) return rc; }
+        for (auto& g : c->wf->graphs) cudaGraphExecDestroy(g.exec);
+        c->wf->graphs.clear();
+    }
     if (pd.calls == 0) PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 64, s));                   // totals add up over pending calls
     pd.stream = s;
     const bool counted = (p->flags & PB_RENDER_COUNTED) != 0u, timing = (p->flags & PB_RENDER_STAGE_TIMING) != 0u;
@@ -559,11 +580,6 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     record(pd.whole);
     const unsigned g_trace = (unsigned)c->sm_count * 8u, g_shade = (unsigned)c->sm_count * 8u;
     const bool use_graph = c->use_graphs && !counted && !timing;   // event records stay on the plain launch path
-    if (!c->wf->graphs.empty() && c->wf->graphs.front().epoch != c->scene_epoch) {
-        if (pd.calls) { rc = wavefront_wait(c); if (rc != PB_OK) return rc; pd.stream = s; PB_CUDA_TRY(c, cudaMemsetAsync(st.totals, 0, 64, s)); }
-        for (auto& g : c->wf->graphs) cudaGraphExecDestroy(g.exec);
-        c->wf->graphs.clear();
-    }
     uint32_t launches = 0;
     for (uint32_t k0 = 0; k0 < p->sample_count; k0 += K) {
         const uint32_t kw = std::min(K, p->sample_count - k0);
@@ -576,21 +592,21 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
         auto enqueue_wave = [&]() {
             k_generate<<<(n_paths + 255) / 256, 256, 0, s>>>(st, sc, n_paths);
             int cur = 0;
-            for (uint32_t b = 0; b < std::max(1u, p->max_depth); ++b) {
+            for (uint32_t b = 0; b < n_bounces; ++b) {
                 k_prepare<<<1, 1, 0, s>>>(st, cur, n_paths, b == 0 ? 1 : 0);
                 mark(ev_ext);
                 if (counted) k_extend<true><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
                 else k_extend<false><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
                 mark(ev_ext);
                 mark(ev_shd);
-                k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, d_albedo, d_normal);
-                launch_shade<1>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-                launch_shade<2>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-                launch_shade<3>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-                launch_shade<4>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-                launch_shade<5>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-                launch_shade<6>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
-                launch_shade<7>(st, sc, cur, k_aov, d_albedo, d_normal, g_shade, s);
+                k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, aov);
+                launch_shade<1>(st, sc, cur, k_aov, aov, g_shade, s);
+                launch_shade<2>(st, sc, cur, k_aov, aov, g_shade, s);
+                launch_shade<3>(st, sc, cur, k_aov, aov, g_shade, s);
+                launch_shade<4>(st, sc, cur, k_aov, aov, g_shade, s);
+                launch_shade<5>(st, sc, cur, k_aov, aov, g_shade, s);
+                launch_shade<6>(st, sc, cur, k_aov, aov, g_shade, s);
+                launch_shade<7>(st, sc, cur, k_aov, aov, g_shade, s);
                 k_after_shade<<<1, 1, 0, s>>>(st);
                 mark(ev_shd);
                 mark(ev_con);
@@ -601,19 +617,19 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
             }
             k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), p->width, p->height, kw);
         };
-        launches += 2u + 12u * std::max(1u, p->max_depth);
+        launches += 2u + 12u * n_bounces;
         cudaGraphExec_t exec = nullptr;
         if (use_graph) {
             for (auto& g : c->wf->graphs)
                 if (g.epoch == c->scene_epoch && g.width == p->width && g.height == p->height && g.max_depth == p->max_depth &&
-                    g.stride == sc.stride && g.kw == kw && g.k_aov == k_aov && g.d_sum == d_sum && g.d_albedo == d_albedo && g.d_normal == d_normal)
+                    g.stride == sc.stride && g.kw == kw && g.k_aov == k_aov && g.d_sum == d_sum && g.d_albedo == d_albedo && g.d_normal == d_normal && g.d_test == d_test)
                     exec = g.exec;
             if (!exec && cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
                 enqueue_wave();
                 cudaGraph_t graph = nullptr;
                 if (cudaStreamEndCapture(s, &graph) == cudaSuccess && graph && cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess) {
                     if (c->wf->graphs.size() >= 8 && pd.calls == 0) { cudaGraphExecDestroy(c->wf->graphs.front().exec); c->wf->graphs.erase(c->wf->graphs.begin()); }
-                    c->wf->graphs.push_back({c->scene_epoch, p->width, p->height, p->max_depth, sc.stride, kw, k_aov, d_sum, d_albedo, d_normal, exec});
+                    c->wf->graphs.push_back({c->scene_epoch, p->width, p->height, p->max_depth, sc.stride, kw, k_aov, d_sum, d_albedo, d_normal, d_test, exec});
                 } else {
                     exec = nullptr;
                 }

@@ -24,7 +24,17 @@ void B200PTPass::fail(const char* what) noexcept {
 // pt_pass.cpp:211-223
 void B200PTPass::BindingEventCallback() noexcept {
     m_system->Bind(EWorldEvent::CameraChange, [this](void*) { m_dirty = true; });
-    m_system->Bind(EWorldEvent::RenderInstanceUpdate, [this](void*) { m_dirty = true; });
+    // pt_pass.cpp:216-218 only sets the dirty flag and OnRun re-fetches the IAS handle with the new instance
+    // transforms (GetIASHandle(2, true), pt_pass.cpp:46 -> IASManager::UpdateInstance, ias_manager.cpp:187-205); here the
+    // moved object's id and matrix are recorded and handed to pb_update_instance before the next pb_render
+    m_system->Bind(EWorldEvent::RenderInstanceUpdate, [this](void* p) {
+        if (auto* ro = static_cast<world::RenderObject*>(p)) {
+            bool found = false;
+            for (auto& m : m_moved) if (m.first == ro->index) { m.second = ro->transform.matrix; found = true; }
+            if (!found) m_moved.emplace_back(ro->index, ro->transform.matrix);
+        }
+        m_dirty = true;
+    });
     m_system->Bind(ESystemEvent::SceneLoad, [this](void* p) { SetScene(static_cast<world::World*>(p)); });
 }
 
@@ -44,7 +54,9 @@ void B200PTPass::SetScene(world::World* world) noexcept {
     m_accum = bm.AllocBuffer({"pt accum buffer", EBufferFlag::None, m_w, m_h, sizeof(float) * 4});   // sums.xyz + frame count.w
     m_albedo = bm.AllocBuffer({"albedo", EBufferFlag::AllowDisplay, m_w, m_h, sizeof(float) * 3});
     m_normal = bm.AllocBuffer({"normal", EBufferFlag::AllowDisplay, m_w, m_h, sizeof(float) * 3});
-    if (!m_frame || !m_accum || !m_albedo || !m_normal) { m_error = "output buffer allocation failed"; m_system->last_error = m_error; return; }
+    m_test = bm.AllocBuffer({"test", EBufferFlag::AllowDisplay, m_w, m_h, sizeof(float)});                // pt_pass.cpp:144-146
+    m_moved.clear();
+    if (!m_frame || !m_accum || !m_albedo || !m_normal || !m_test) { m_error = "output buffer allocation failed"; m_system->last_error = m_error; return; }
     m_dirty = true;
 }
 
@@ -52,6 +64,9 @@ void B200PTPass::SetScene(world::World* world) noexcept {
 void B200PTPass::OnRun() noexcept {
     if (!m_ctx || !m_world || !m_error.empty()) return;
     if (m_dirty) {
+        for (auto& mv : m_moved)
+            if (pb_update_instance(m_ctx, mv.first, mv.second.e) != PB_OK) return fail("pb_update_instance");
+        m_moved.clear();
         const pupil::host::Mat4 s2c = m_world->camera.GetSampleToCameraMatrix(), c2w = m_world->camera.GetToWorldMatrix();
         if (pb_set_camera(m_ctx, s2c.e, c2w.e) != PB_OK) return fail("pb_set_camera");
         m_sample_cnt = 0;
@@ -65,8 +80,9 @@ void B200PTPass::OnRun() noexcept {
     p.sample_count = frames_per_run;
     p.sample_stride = 1;
     p.flags = (m_sample_cnt == 0 || !accumulated_flag) ? PB_RENDER_CLEAR : 0u;
-    if (pb_render(m_ctx, &p, static_cast<float*>(m_accum->cuda_ptr), static_cast<float*>(m_albedo->cuda_ptr),
-                  static_cast<float*>(m_normal->cuda_ptr), m_stream) != PB_OK) return fail("pb_render");
+    const pb_render_targets tg{static_cast<float*>(m_accum->cuda_ptr), static_cast<float*>(m_albedo->cuda_ptr),
+                               static_cast<float*>(m_normal->cuda_ptr), static_cast<float*>(m_test->cuda_ptr)};
+    if (pb_render_ex(m_ctx, &p, &tg, m_stream) != PB_OK) return fail("pb_render_ex");
     if (pb_resolve(m_ctx, static_cast<const float*>(m_accum->cuda_ptr), static_cast<float*>(m_frame->cuda_ptr), m_w * m_h, 0, m_stream) != PB_OK)
         return fail("pb_resolve");
     if (accumulated_flag) m_sample_cnt += frames_per_run;   // sample_cnt += accumulated_flag (pt_pass.cpp:55)

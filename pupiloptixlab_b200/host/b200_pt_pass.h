@@ -1,11 +1,13 @@
 // b200_pt_pass.h — the path-tracing pass behind the reference's plug-in interface, driving
 // libpupil_b200.so through its C ABI.  Replaces Pupil::pt::PTPass
 // (example/path_tracer/pt_pass.h:21-41, pt_pass.cpp:29-237): same constructor / OnRun / SetScene
-// contract, same named output buffers ("final result", "pt accum buffer", "albedo", "normal"), same
+// contract, same named output buffers ("final result", "pt accum buffer", "albedo", "normal", "test"), same
 // dirty handling (camera or instance change => sample count and seed restart, pt_pass.cpp:40-49).
 #pragma once
 #include "../../include/pupil_b200.h"
 #include "system.h"
+
+#include <utility>
 
 namespace Pupil::pt {
 
@@ -30,7 +32,8 @@ private:
     pb_ctx* m_ctx = nullptr;
     cudaStream_t m_stream = nullptr;
     world::World* m_world = nullptr;
-    Buffer *m_frame = nullptr, *m_accum = nullptr, *m_albedo = nullptr, *m_normal = nullptr;
+    Buffer *m_frame = nullptr, *m_accum = nullptr, *m_albedo = nullptr, *m_normal = nullptr, *m_test = nullptr;
+    std::vector<std::pair<uint32_t, pupil::host::Mat4>> m_moved;   // instances whose transform changed since the last OnRun
     uint32_t m_w = 0, m_h = 0, m_sample_cnt = 0, m_random_seed = 0;
     bool m_dirty = true;
     std::string m_error;

@@ -113,6 +113,65 @@ PH_API int ph_image_save_png8(const char* path, const uint8_t* rgba8, uint32_t w
     return pupil::host::save_png8(path, rgba8, (int)w, (int)h, g_err) ? PB_OK : PB_ERR_INVALID;
 }
 
+struct ph_session {
+    Pupil::System system;
+    std::unique_ptr<Pupil::pt::B200PTPass> pass;
+};
+
+PH_API int ph_session_create(const char* xml_path, int device, ph_session** out) {
+    using namespace Pupil;
+    g_err.clear();
+    if (!xml_path || !out) return PB_ERR_INVALID;
+    *out = nullptr;
+    auto s = std::make_unique<ph_session>();
+    s->system.Init(false);
+    s->pass = std::make_unique<pt::B200PTPass>(&s->system, device);
+    if (!s->pass->ok()) { g_err = s->pass->error(); return PB_ERR_NO_DEVICE; }
+    s->system.AddPass(s->pass.get());
+    if (!s->system.SetScene(xml_path) || !s->pass->ok()) {
+        g_err = s->system.last_error.empty() ? s->pass->error() : s->system.last_error;
+        return PB_ERR_INVALID;
+    }
+    *out = s.release();
+    return PB_OK;
+}
+PH_API void ph_session_destroy(ph_session* s) {
+    if (!s) return;
+    s->pass.reset();          // the pass's buffers belong to the system's BufferManager: drop the pass first
+    s->system.Destroy();
+    delete s;
+}
+PH_API int ph_session_run(ph_session* s, uint32_t frames) {
+    if (!s) return PB_ERR_INVALID;
+    s->system.RunFrames(frames);
+    if (!s->pass->ok()) { g_err = s->pass->error(); return PB_ERR_CUDA; }
+    return PB_OK;
+}
+PH_API int ph_session_move_object(ph_session* s, uint32_t index, const float to_world[16]) {
+    if (!s || !to_world) return PB_ERR_INVALID;
+    auto ros = s->system.world.GetRenderobjects();
+    if (index >= ros.size()) { g_err = "render object index out of range"; return PB_ERR_INVALID; }
+    pupil::host::Transform t;
+    std::memcpy(t.matrix.e, to_world, 64);
+    ros[index]->UpdateTransform(t);
+    return PB_OK;
+}
+PH_API int ph_session_read(ph_session* s, const char* name, void* dst, uint64_t bytes) {
+    if (!s || !name || !dst) return PB_ERR_INVALID;
+    Pupil::Buffer* b = s->system.buffers.GetBuffer(name);
+    if (!b) { g_err = std::string("no buffer named '") + name + "'"; return PB_ERR_INVALID; }
+    if (bytes != b->size_in_byte()) { g_err = "size mismatch for buffer '" + std::string(name) + "'"; return PB_ERR_INVALID; }
+    if (cudaMemcpy(dst, b->cuda_ptr, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) { g_err = "cudaMemcpy failed"; return PB_ERR_CUDA; }
+    return PB_OK;
+}
+PH_API int ph_session_film(const ph_session* s, uint32_t* w, uint32_t* h) {
+    if (!s || !s->system.world.scene) return PB_ERR_INVALID;
+    if (w) *w = static_cast<uint32_t>(s->system.world.scene->film_w);
+    if (h) *h = static_cast<uint32_t>(s->system.world.scene->film_h);
+    return PB_OK;
+}
+PH_API uint32_t ph_session_sample_count(const ph_session* s) { return s ? s->pass->sample_cnt() : 0u; }
+
 PH_API int ph_run_path_tracer(const char* xml_path, int device, uint32_t frames, float* final_rgba, float* albedo_rgb,
                               float* normal_rgb, uint32_t* out_w, uint32_t* out_h) {
     using namespace Pupil;

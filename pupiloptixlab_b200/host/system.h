@@ -93,18 +93,62 @@ enum class ESystemEvent { Quit, Precompute, StartRendering, StopRendering, Scene
 enum class EWorldEvent { CameraChange, CameraMove, CameraFovChange, CameraViewChange, RenderInstanceTransform, RenderInstanceUpdate, RenderInstanceRemove };
 
 namespace world {
-// what the pass pulls from World (pt_pass.cpp:107-150): the loaded scene and the camera helper
+class World;
+// world::RenderObject (framework/world/render_object.h:11-31) reduced to what the event contract needs: identity, the
+// current transform and UpdateTransform / ApplyTransform, which raise EWorldEvent::RenderInstanceTransform with `this`
+// as the payload exactly as render_object.cpp:46-54 does.  `index` = position in scene->shape_instances = object id
+// behind the C ABI (World keeps the same mapping in m_ro_in_scene_index, world.cpp:46-47).
+struct RenderObject {
+    std::string name;
+    uint32_t index = 0;
+    pupil::host::Transform transform;
+    World* world = nullptr;
+    void UpdateTransform(const pupil::host::Transform& new_transform) noexcept;
+    void ApplyTransform(const pupil::host::Transform& new_transform) noexcept;
+};
+
+// what the pass pulls from World (pt_pass.cpp:107-150): the loaded scene, the camera helper, the render objects
 class World {
 public:
     std::unique_ptr<pupil::host::Scene> scene;
     pupil::host::Camera camera;
+    std::function<void(EWorldEvent, void*)> dispatch;   // set by System: the reference's EventDispatcher is a global
     bool LoadScene(const std::string& path, std::string& err) noexcept {
         scene = std::make_unique<pupil::host::Scene>();
         if (!pupil::host::load_scene_xml_file(path, *scene, err)) { scene.reset(); return false; }
         camera = scene->camera();
+        m_ros.clear();
+        for (size_t i = 0; i < scene->shape_instances.size(); ++i) {   // world.cpp:115-127: one RenderObject per instance
+            auto ro = std::make_unique<RenderObject>();
+            ro->name = scene->shape_instances[i].name; ro->index = static_cast<uint32_t>(i);
+            ro->transform = scene->shape_instances[i].transform; ro->world = this;
+            m_ros.push_back(std::move(ro));
+        }
         return true;
     }
+    std::vector<RenderObject*> GetRenderobjects() noexcept {   // world.cpp:141-148
+        std::vector<RenderObject*> v;
+        for (auto& r : m_ros) v.push_back(r.get());
+        return v;
+    }
+    // the RenderInstanceTransform handler of world.cpp:45-54: the scene's instance takes the new transform, then
+    // RenderInstanceUpdate goes out (emitter tables are rebuilt by pb_update_instance on the pass side)
+    void OnInstanceTransform(RenderObject* ro) noexcept {
+        if (!scene || !ro || ro->index >= scene->shape_instances.size()) return;
+        scene->shape_instances[ro->index].transform = ro->transform;
+        if (dispatch) dispatch(EWorldEvent::RenderInstanceUpdate, ro);
+    }
+private:
+    std::vector<std::unique_ptr<RenderObject>> m_ros;
 };
+inline void RenderObject::UpdateTransform(const pupil::host::Transform& new_transform) noexcept {
+    transform = new_transform;
+    if (world && world->dispatch) world->dispatch(EWorldEvent::RenderInstanceTransform, this);
+}
+inline void RenderObject::ApplyTransform(const pupil::host::Transform& new_transform) noexcept {
+    transform.matrix = pupil::host::mul(new_transform.matrix, transform.matrix);
+    if (world && world->dispatch) world->dispatch(EWorldEvent::RenderInstanceTransform, this);
+}
 }  // namespace world
 
 class System {
@@ -115,6 +159,12 @@ public:
     world::World world;
     std::string last_error;
 
+    System() {
+        world.dispatch = [this](EWorldEvent e, void* p) { Dispatch(e, p); };
+        Bind(EWorldEvent::RenderInstanceTransform, [this](void* p) { world.OnInstanceTransform(static_cast<world::RenderObject*>(p)); });
+    }
+    System(const System&) = delete;
+    System& operator=(const System&) = delete;
     void Init(bool has_window = false) noexcept { (void)has_window; /* headless only: system.cpp:55-59 */ }
     void AddPass(Pass* pass) noexcept {                 // system.cpp:129-134: not owned
         if (pass->tag & EPassTag::Pre) m_pre_passes.push_back(pass);

@@ -122,6 +122,63 @@ class Scene:
             raise HostError(f"{self.lib.ph_last_error().decode()}: {ctx.api._last_error(ctx.h).decode()}")
 
 
+class Session:
+    """ph_session: a headless System + B200PTPass kept alive between calls (render, move an object, render, read)."""
+    BUFFERS = {"final result": 4, "pt accum buffer": 4, "albedo": 3, "normal": 3, "test": 1}
+
+    def __init__(self, xml_path: str, device: int = 0):
+        self.lib = load()
+        L = self.lib
+        L.ph_session_create.argtypes = [C.c_char_p, _i32, C.POINTER(_vp)]
+        L.ph_session_destroy.argtypes = [_vp]
+        L.ph_session_run.argtypes = [_vp, _u32]
+        L.ph_session_move_object.argtypes = [_vp, _u32, _fpp]
+        L.ph_session_read.argtypes = [_vp, C.c_char_p, _vp, C.c_uint64]
+        L.ph_session_film.argtypes = [_vp, C.POINTER(_u32), C.POINTER(_u32)]
+        L.ph_session_sample_count.argtypes = [_vp]
+        L.ph_session_sample_count.restype = _u32
+        self.h = _vp()
+        rc = L.ph_session_create(xml_path.encode(), device, C.byref(self.h))
+        if rc != 0:
+            raise HostError(f"ph_session_create failed ({rc}): {L.ph_last_error().decode()}")
+        w, h = _u32(), _u32()
+        L.ph_session_film(self.h, C.byref(w), C.byref(h))
+        self.w, self.h_px = w.value, h.value
+
+    def close(self):
+        if self.h:
+            self.lib.ph_session_destroy(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def run(self, frames: int):
+        rc = self.lib.ph_session_run(self.h, frames)
+        if rc != 0:
+            raise HostError(f"ph_session_run failed ({rc}): {self.lib.ph_last_error().decode()}")
+
+    def move_object(self, index: int, to_world):
+        m = np.ascontiguousarray(to_world, np.float32).reshape(16).copy()
+        rc = self.lib.ph_session_move_object(self.h, index, capi._fp(m))
+        if rc != 0:
+            raise HostError(f"ph_session_move_object failed ({rc}): {self.lib.ph_last_error().decode()}")
+
+    def read(self, name: str) -> np.ndarray:
+        ch = self.BUFFERS[name]
+        out = np.zeros((self.h_px, self.w, ch) if ch > 1 else (self.h_px, self.w), np.float32)
+        rc = self.lib.ph_session_read(self.h, name.encode(), out.ctypes.data, out.nbytes)
+        if rc != 0:
+            raise HostError(f"ph_session_read({name}) failed ({rc}): {self.lib.ph_last_error().decode()}")
+        return out
+
+    def sample_count(self) -> int:
+        return int(self.lib.ph_session_sample_count(self.h))
+
+
 def load_image(path: str) -> np.ndarray:
     """BitmapTexture::Load: (h, w, 4) float32 texels, row 0 = top."""
     lib = load()

@@ -221,6 +221,56 @@ def cornell_box(ctx: capi.Context, width=256, height=256, variant="diffuse") -> 
     return {"width": width, "height": height, "objects": objs, "materials": mats}
 
 
+def edge_scene(ctx: capi.Context, width=160, height=120, env=True, emitters=True) -> dict:
+    """Branches of the hot path that the Cornell variants do not reach (parity gaps):
+    constant environment emitter (emitter/env.h:67-86), flip_normals / flip_tex_coords (geometry.h:62-75; the latter is
+    the default of every imported .obj), meshes without vertex normals (cross-product branch, geometry.h:57-60) and
+    without uvs, nonlinear plastic / rough plastic (plastic.h:38, rough_plastic.h:44), a dielectric with
+    int_ior < ext_ior (eta < 1), non-uniformly scaled spheres (one of them an area emitter, sphere.h:14-42).
+    `emitters=False` leaves the scene without any light (NEE has nothing to select)."""
+    ctx.scene_begin()
+    M = capi.make_material
+    chk = capi.checker_texture((0.8, 0.25, 0.1), (0.15, 0.3, 0.85), 6, 6)
+    m_floor = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True, reflectance=chk))
+    m_wall = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True, reflectance=(0.7, 0.68, 0.6)))
+    m_one_sided = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=False, reflectance=(0.3, 0.6, 0.35)))
+    m_plastic_nl = ctx.add_material(M(capi.MAT_PLASTIC, twosided=True, nonlinear=True, int_ior=1.5, ext_ior=1.0, reflectance=chk,
+                                      specular_reflectance=(0.9, 0.9, 0.8)))
+    m_rplastic_nl = ctx.add_material(M(capi.MAT_ROUGH_PLASTIC, twosided=True, nonlinear=True, alpha=0.15, int_ior=1.49, ext_ior=1.0,
+                                       reflectance=(0.5, 0.5, 0.1)))
+    m_glass_inv = ctx.add_material(M(capi.MAT_DIELECTRIC, int_ior=1.0, ext_ior=1.5))
+    m_rglass_inv = ctx.add_material(M(capi.MAT_ROUGH_DIELECTRIC, int_ior=1.0, ext_ior=1.33, alpha=0.2))
+    m_black = ctx.add_material(M(capi.MAT_DIFFUSE, twosided=True, reflectance=(0, 0, 0)))
+    objs = {}
+    # floor with uvs, v flipped (ShapeInstance::flip_tex_coords)
+    objs["floor"] = ctx.add_trimesh(RECT_POS, RECT_NRM, RECT_UV, RECT_IDX, rotate(1, 0, 0, -90) @ scale(1.5, 1.5, 1), capi.SHAPE_FLIP_TEX_COORDS, m_floor)
+    # back wall without normals and without uvs
+    objs["back"] = ctx.add_trimesh(RECT_POS, None, None, RECT_IDX, translate(0, 1, -1.5) @ scale(1.5, 1, 1), 0, m_wall)
+    # left wall: one-sided material, geometric normal points away from the room, flip_normals turns it back
+    objs["left"] = ctx.add_trimesh(RECT_POS, RECT_NRM, RECT_UV, RECT_IDX, translate(-1.5, 1, 0) @ rotate(0, 1, 0, -90) @ scale(1.5, 1, 1),
+                                   capi.SHAPE_FLIP_NORMALS, m_one_sided)
+    # cube without normals (uvs kept): nonlinear plastic with a checkerboard reflectance
+    objs["cube"] = ctx.add_trimesh(CUBE_POS, None, CUBE_UV, CUBE_IDX, translate(-0.7, 0.3, -0.4) @ rotate(0, 1, 0, 30) @ scale(0.3, 0.3, 0.3),
+                                   capi.SHAPE_FLIP_TEX_COORDS, m_plastic_nl)
+    # a cube with normals but no uvs, flip_normals + two-sided material
+    objs["cube2"] = ctx.add_trimesh(CUBE_POS, CUBE_NRM, None, CUBE_IDX, translate(0.9, 0.2, -0.7) @ rotate(0, 1, 0, -20) @ scale(0.2, 0.2, 0.2),
+                                    capi.SHAPE_FLIP_NORMALS, m_rplastic_nl)
+    objs["glass"] = add_sphere(ctx, (0.1, 0.35, 0.2), 0.35, m_glass_inv)
+    # non-uniformly scaled, rotated spheres
+    objs["ellipsoid"] = ctx.add_sphere(translate(0.85, 0.22, 0.45) @ rotate(1, 1, 0, 40) @ scale(0.35, 0.15, 0.22), 0, m_rplastic_nl)
+    objs["ellipsoid_glass"] = ctx.add_sphere(translate(-0.55, 0.9, 0.1) @ rotate(0, 0, 1, 25) @ scale(0.3, 0.12, 0.2), capi.SHAPE_FLIP_NORMALS, m_rglass_inv)
+    if emitters:
+        objs["ellipsoid_light"] = ctx.add_sphere(translate(-0.2, 1.6, -0.6) @ scale(0.12, 0.05, 0.09), 0, m_black, capi.rgb_texture(25, 22, 18))
+        objs["light"] = ctx.add_trimesh(RECT_POS, RECT_NRM, RECT_UV, RECT_IDX, translate(0.6, 1.9, 0.0) @ rotate(1, 0, 0, 90) @ scale(0.2, 0.2, 1), 0, m_black,
+                                        capi.rgb_texture(12, 12, 14))
+        if env:
+            ctx.set_env(capi.env_const(0.45, 0.55, 0.8))
+    to_world = lookat_to_world((0.2, 1.3, 3.4), (0.0, 0.6, 0.0), (0, 1, 0))
+    set_perspective_camera(ctx, 42.0, width, height, to_world)
+    ctx.commit()
+    return {"width": width, "height": height, "objects": objs}
+
+
 def procedural_bitmap(w: int, h: int, seed: int) -> np.ndarray:
     """(h, w, 4) float RGBA test pattern in [0.05, 0.95]: smooth gradients + seeded blocks (no image files)."""
     rng = np.random.RandomState(seed)

@@ -13,6 +13,8 @@
 #include "../../pupiloptixlab_b200/csrc/pb_host_math.h"
 #include "../../pupiloptixlab_b200/csrc/pb_scene.cuh"
 #include "../../pupiloptixlab_b200/csrc/pb_slots.cuh"
+#include "../../pupiloptixlab_b200/csrc/pb_host_prep.h"
+#include "../devsim/table_body.h"
 
 using namespace pb;
 
@@ -151,6 +153,13 @@ void hs_trace_any(HS* h, const float* rays, uint64_t n, uint8_t* occ) {
         traverse<true, true>(sc, {r[0], r[1], r[2]}, {r[4], r[5], r[6]}, r[3], r[7], hit, st, &h->cnt);
         occ[i] = hit.prim != 0xFFFFFFFFu;
     }
+}
+// per-BSDF known-answer table computed by the product's pb_bsdf.cuh on the CPU (tests/devsim/table_body.h)
+int hs_bsdf_table(const pb_material* mat, const float* wo, const uint32_t* seeds, uint32_t n, float* out) {
+    if (!mat) return 1;
+    const MatRec m = prep::mat_rec(*mat);
+    for (uint32_t i = 0; i < n; ++i) bsdf_table_entry_any(m, wo + 3 * i, seeds[i], out + 16 * i);
+    return 0;
 }
 // wave slot -> (frame, pixel) for every slot of a wave of K frames of a w x h film, and the inverse used by k_accumulate
 void hs_slot_tables(uint32_t w, uint32_t h, uint32_t K, uint32_t* frame_of_slot, uint32_t* pixel_of_slot, uint32_t* slot_of_kj) {
