@@ -20,6 +20,7 @@
 #include <cstring>
 
 #include "orc_scene.h"
+#include "orc_cwbvh.h"
 #include "backend_ref.h"
 #include "../include/pupil_b200.h"
 
@@ -81,7 +82,7 @@ struct BNode {
     uint32_t leaf;
 };
 
-struct Counters { uint64_t rays_closest = 0, rays_any = 0; };
+struct Counters { uint64_t rays_closest = 0, rays_any = 0; CwCounts cw_closest, cw_any; uint64_t cw_mismatch = 0; };
 
 struct Ctx {
     std::string err;
@@ -106,6 +107,8 @@ struct Ctx {
     EmitterRec env;
     std::vector<float> env_row_cdf, env_col_cdf, env_row_weight;
     pb_stats stats{};
+    CwBvh cw;                         // the product's committed BVH, imported for the visit-count traversal (orc_cwbvh.h)
+    uint64_t cw_mismatch = 0;         // rays whose CWBVH-traversal hit differed from the oracle's own BVH (must stay 0)
 };
 
 static Texture make_tex(Ctx* c, const pb_texture& t) {
@@ -271,6 +274,19 @@ static Hit bvh_trace(const Ctx* c, const Ray& r) {
         }
     }
     return best;
+}
+
+// ordered, t-culled traversal of the imported 8-wide BVH with this scene's own acceptance test
+template<bool ANY>
+static Hit cw_trace_ctx(const Ctx* c, const Ray& r, CwCounts& cnt) {
+    const RayPre pre = ray_pre(r);
+    return cw_trace<ANY>(c->cw, r, cnt, [&](uint32_t gid, float& t, float& u, float& v) {
+        return gid < c->prims.size() && prim_accept(c, r, pre, gid, t, u, v);
+    });
+}
+static inline bool same_hit(const Hit& a, const Hit& b) {
+    if (a.prim != b.prim) return false;
+    return a.prim == kMiss || (f2u(a.t) == f2u(b.t) && f2u(a.u) == f2u(b.u) && f2u(a.v) == f2u(b.v));
 }
 
 // ---------------------------------------------------------------------------------- commit
@@ -581,6 +597,7 @@ static f3 path_radiance(const Ctx* c, const pb_render_params& rp, uint32_t x, ui
     f3 radiance = mk3(0.f), env_radiance = mk3(0.f), throughput = mk3(1.f);
     float env_pdf = 0.f;
     bool done = false;
+    const bool count_cw = (rp.flags & PB_RENDER_COUNTED) && !c->cw.empty();   // visit counts on the imported product BVH
 
     float jx = B::rng_next(rng), jy = B::rng_next(rng);  // main.cu:55
     f2 subpixel = {(static_cast<float>(x) + jx) / static_cast<float>(w), (static_cast<float>(y) + jy) / static_cast<float>(h)};
@@ -598,6 +615,7 @@ static f3 path_radiance(const Ctx* c, const pb_render_params& rp, uint32_t x, ui
         Ray r{o, 0.001f, dir, 1e16f};
         cnt.rays_closest++;
         Hit hh = bvh_trace<false>(c, r);
+        if (count_cw && !same_hit(cw_trace_ctx<false>(c, r, cnt.cw_closest), hh)) cnt.cw_mismatch++;
         if (hh.prim == kMiss) {  // __miss__default, main.cu:196-212
             if (c->env.type != kEmNone) {
                 f3 rd = normalize(dir);
@@ -645,6 +663,7 @@ static f3 path_radiance(const Ctx* c, const pb_render_params& rp, uint32_t x, ui
                 Ray sr{local_hit.geo.position, 0.001f, es.wi, es.distance - 0.001f};
                 cnt.rays_any++;
                 occluded = bvh_trace<true>(c, sr).prim != kMiss;
+                if (count_cw && (cw_trace_ctx<true>(c, sr, cnt.cw_any).prim != kMiss) != occluded) cnt.cw_mismatch++;
             }
             if (!occluded) {
                 BsdfRecord er;
@@ -695,7 +714,7 @@ static f3 path_radiance(const Ctx* c, const pb_render_params& rp, uint32_t x, ui
 
 // Window [x0, x0+ww) x [y0, y0+wh) of the film (the whole film by default): output buffers are window-sized,
 // seeds stay those of the full film (pixel_index = y * width + x), so a crop of a large film costs only its pixels.
-struct Window { uint32_t x0, y0, w, h; };
+struct Window { uint32_t x0, y0, w, h, step = 1; };   // pixel (x0 + i * step, y0 + j * step), i < w, j < h
 template<class B>
 static int render(Ctx* c, const pb_render_params* rp, float* sum, float* albedo, float* normal, float* test = nullptr,
                   const Window* win = nullptr) {
@@ -705,16 +724,16 @@ static int render(Ctx* c, const pb_render_params* rp, float* sum, float* albedo,
     if (rp->flags & PB_RENDER_CLEAR) memset(sum, 0, npx * 16);
     uint32_t stride = rp->sample_stride ? rp->sample_stride : 1;
     auto t0 = std::chrono::steady_clock::now();
-    uint64_t rc = 0, ra = 0;
+    uint64_t rc = 0, ra = 0, cn = 0, ct = 0, cs = 0, an = 0, at = 0, as = 0, mm = 0;
     for (uint32_t s = 0; s < rp->sample_count; ++s) {
         uint32_t seed = rp->first_sample + s * stride;
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rc, ra)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rc, ra, cn, ct, cs, an, at, as, mm)
         for (int yy = 0; yy < (int)W.h; ++yy) {
             Counters cnt;
             for (uint32_t xx = 0; xx < W.w; ++xx) {
                 f3 a, n;
                 float tv = 0.f;
-                f3 L = path_radiance<B>(c, *rp, W.x0 + xx, W.y0 + (uint32_t)yy, seed, a, n, tv, cnt);
+                f3 L = path_radiance<B>(c, *rp, W.x0 + xx * W.step, W.y0 + (uint32_t)yy * W.step, seed, a, n, tv, cnt);
                 size_t p = (size_t)yy * W.w + xx;
                 sum[4 * p + 0] += L.x; sum[4 * p + 1] += L.y; sum[4 * p + 2] += L.z; sum[4 * p + 3] += 1.f;
                 if (albedo) { albedo[3 * p] = a.x; albedo[3 * p + 1] = a.y; albedo[3 * p + 2] = a.z; }
@@ -722,8 +741,14 @@ static int render(Ctx* c, const pb_render_params* rp, float* sum, float* albedo,
                 if (test) test[p] = tv;
             }
             rc += cnt.rays_closest; ra += cnt.rays_any;
+            cn += cnt.cw_closest.nodes; ct += cnt.cw_closest.tris; cs += cnt.cw_closest.spheres;
+            an += cnt.cw_any.nodes; at += cnt.cw_any.tris; as += cnt.cw_any.spheres; mm += cnt.cw_mismatch;
         }
     }
+    c->stats.node_visits = cn; c->stats.prim_tests_tri = ct; c->stats.prim_tests_sphere = cs;
+    c->stats.node_visits_any = an; c->stats.prim_tests_tri_any = at; c->stats.prim_tests_sphere_any = as;
+    c->cw_mismatch = mm;
+    if (mm) { c->err = "the ordered traversal of the imported BVH disagrees with the oracle's own BVH on " + std::to_string(mm) + " rays"; return PB_ERR_INVALID; }
     auto t1 = std::chrono::steady_clock::now();
     c->stats.rays_closest = rc; c->stats.rays_any = ra;
     c->stats.samples = (uint64_t)npx * rp->sample_count;
@@ -828,6 +853,7 @@ ORC_API int orc_set_camera(orc_ctx* c, const float s2c[16], const float c2w[16])
     return PB_OK;
 }
 ORC_API int orc_scene_commit(orc_ctx* c) {
+    c->cw = CwBvh{};   // an imported product BVH belongs to the scene it was exported from
     CHECK(c->in_scene, "orc_scene_commit without scene_begin");
     auto t0 = std::chrono::steady_clock::now();
     int rc;
@@ -865,6 +891,74 @@ ORC_API int orc_trace_any(orc_ctx* c, const pb_ray* rays, uint64_t n, uint8_t* o
     for (long long i = 0; i < (long long)n; ++i) occluded[i] = bvh_trace<true>(c, to_ray(rays[i])).prim != kMiss;
     c->stats.rays_any = n;
     c->stats.last_trace_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return PB_OK;
+}
+// ---- the product's committed BVH (pb_export_bvh) read by the oracle: import, then an ordered t-culled traversal that
+// yields the visit counts SURVEY 8(d) defines B_ray on.  Import checks the leaf records against this scene's own
+// world-space primitives bit for bit (same ids, same vertices / centre + extents, every primitive exactly once).
+ORC_API int orc_import_cwbvh(orc_ctx* c, const void* nodes80, uint64_t n_nodes, const void* prims48, uint64_t n_prims) {
+    CHECK(c->committed, "scene not committed");
+    CHECK(n_prims == c->prims.size(), "primitive count differs from the oracle's scene");
+    CHECK((nodes80 && prims48) || n_prims == 0, "null BVH pointers");
+    CwBvh& b = c->cw;
+    b.nodes.assign((const uint8_t*)nodes80, (const uint8_t*)nodes80 + 80 * n_nodes);
+    b.prims.assign((const float*)prims48, (const float*)prims48 + 12 * n_prims);
+    b.n_nodes = n_nodes; b.n_prims = n_prims; b.n_leaf_slots = 0;
+    std::vector<uint8_t> seen(n_prims, 0);
+    for (uint64_t i = 0; i < n_prims; ++i) {
+        const float* r = b.prims.data() + 12 * i;
+        const uint32_t gid = f2u(r[3]), obj = f2u(r[7]), kind = f2u(r[11]);
+        if (gid >= n_prims || seen[gid]) { b = CwBvh{}; c->err = "exported leaf records do not hold every primitive id exactly once"; return PB_ERR_INVALID; }
+        seen[gid] = 1;
+        const Prim& p = c->prims[gid];
+        const float want[9] = {p.v0.x, p.v0.y, p.v0.z, p.v1.x, p.v1.y, p.v1.z, p.v2.x, p.v2.y, p.v2.z};
+        const float got[9] = {r[0], r[1], r[2], r[4], r[5], r[6], r[8], r[9], r[10]};
+        if (kind != p.kind || obj != p.obj || memcmp(want, got, 36) != 0) {
+            b = CwBvh{}; c->err = "exported primitive record " + std::to_string(i) + " differs from the oracle's world-space primitive " + std::to_string(gid);
+            return PB_ERR_INVALID;
+        }
+    }
+    // structure: every node reachable once, child / primitive ranges inside the arrays, leaves cover all primitives
+    std::vector<uint8_t> node_seen(n_nodes, 0);
+    std::vector<uint32_t> todo;
+    uint64_t covered = 0;
+    if (n_nodes) { todo.push_back(0); node_seen[0] = 1; }
+    while (!todo.empty()) {
+        const uint32_t ni = todo.back(); todo.pop_back();
+        const CwNode n = cw_decode(b.nodes.data() + 80ull * ni);
+        uint32_t rank = 0, pcount = 0;
+        for (int s = 0; s < 8; ++s) {
+            const uint32_t lc = cw_leaf_count(n.pmask, s);
+            if ((n.imask >> s) & 1u) {
+                const uint64_t ch = (uint64_t)n.child_base + rank++;
+                if (lc || ch >= n_nodes || node_seen[ch]) { b = CwBvh{}; c->err = "exported BVH is not a tree"; return PB_ERR_INVALID; }
+                node_seen[ch] = 1; todo.push_back((uint32_t)ch);
+            } else if (lc) { pcount += lc; ++b.n_leaf_slots; }
+        }
+        if ((uint64_t)n.prim_base + pcount > n_prims) { b = CwBvh{}; c->err = "exported BVH leaf range outside the primitive array"; return PB_ERR_INVALID; }
+        covered += pcount;
+    }
+    if (covered != n_prims) { b = CwBvh{}; c->err = "exported BVH leaves do not cover every primitive"; return PB_ERR_INVALID; }
+    return PB_OK;
+}
+ORC_API uint64_t orc_cwbvh_leaf_slots(const orc_ctx* c) { return c->cw.n_leaf_slots; }
+// out: pb_hit[n] (closest) or uint8[n] (any); counts[3] = nodes fetched, triangle records tested, sphere records tested
+ORC_API int orc_trace_cwbvh(orc_ctx* c, const pb_ray* rays, uint64_t n, void* out, int any, uint64_t counts[3]) {
+    CHECK(c->committed && !c->cw.empty(), "no imported BVH (orc_import_cwbvh)");
+    uint64_t cn = 0, ct = 0, cs = 0;
+#pragma omp parallel for schedule(dynamic, 1024) reduction(+ : cn, ct, cs)
+    for (long long i = 0; i < (long long)n; ++i) {
+        CwCounts cnt;
+        const Ray r = to_ray(rays[i]);
+        if (any) {
+            ((uint8_t*)out)[i] = cw_trace_ctx<true>(c, r, cnt).prim != kMiss;
+        } else {
+            Hit h = cw_trace_ctx<false>(c, r, cnt);
+            ((pb_hit*)out)[i] = h.prim == kMiss ? pb_hit{rays[i].tmax, 0.f, 0.f, PB_MISS} : pb_hit{h.t, h.u, h.v, h.prim};
+        }
+        cn += cnt.nodes; ct += cnt.tris; cs += cnt.spheres;
+    }
+    if (counts) { counts[0] = cn; counts[1] = ct; counts[2] = cs; }
     return PB_OK;
 }
 // ground truth: O(N) loop over all primitives per ray
@@ -909,11 +1003,12 @@ ORC_API int orc_render_ex(orc_ctx* c, const pb_render_params* p, const pb_render
 }
 // oracle only: a window of the film (window-sized output buffers, full-film seeds)
 ORC_API int orc_render_window(orc_ctx* c, const pb_render_params* p, const pb_render_targets* t, uint32_t x0, uint32_t y0,
-                              uint32_t w, uint32_t h) {
+                              uint32_t w, uint32_t h, uint32_t step) {
     CHECK(c->committed, "scene not committed");
     CHECK(p && t && t->accum_sum_rgba, "null render params / targets");
-    CHECK(w && h && x0 + w <= p->width && y0 + h <= p->height, "window outside the film");
-    const Window win{x0, y0, w, h};
+    if (step == 0) step = 1;
+    CHECK(w && h && x0 + (w - 1) * step < p->width && y0 + (h - 1) * step < p->height, "window outside the film");
+    const Window win{x0, y0, w, h, step};
 #ifdef ORC_WITH_REFERENCE
     if (c->backend == 1) return render<RefBackend>(c, p, t->accum_sum_rgba, t->albedo_rgb, t->normal_rgb, t->test, &win);
 #endif

@@ -40,8 +40,10 @@ def _extend(api: capi.Api) -> capi.Api:
     api._f("rng_stream", i32, [vp, u32, u32, u32, C.POINTER(u32), fpp])
     api._f("bsdf_table", i32, [vp, u32, fpp, C.POINTER(u32), u32, fpp])
     api._f("emitter_table", i32, [vp, u32, fpp, fpp, fpp, u32, fpp])
-    api._f("render_window", i32, [vp, C.POINTER(capi.RenderParams), C.POINTER(capi.RenderTargets), u32, u32, u32, u32])
-    api._f("trace_cwbvh", i32, [vp, vp, u64, vp, u64, vp, u64, vp, C.POINTER(u64), i32], optional=True)
+    api._f("render_window", i32, [vp, C.POINTER(capi.RenderParams), C.POINTER(capi.RenderTargets), u32, u32, u32, u32, u32])
+    api._f("import_cwbvh", i32, [vp, vp, u64, vp, u64])
+    api._f("cwbvh_leaf_slots", u64, [vp])
+    api._f("trace_cwbvh", i32, [vp, vp, u64, vp, i32, C.POINTER(u64)])
     return api
 
 
@@ -84,15 +86,38 @@ class OracleContext(capi.Context):
         self._ck(self.api._trace_any_brute(self.h, rays.ctypes.data, rays.shape[0], occ.ctypes.data), "trace_any_brute")
         return occ
 
-    def render_window(self, width, height, max_depth, first_sample, sample_count, x0, y0, w, h, sample_stride=1):
-        """Window [x0, x0+w) x [y0, y0+h) of a width x height film (full-film seeds): (sum, albedo, normal, test), window-sized."""
-        p = capi.RenderParams(width, height, max_depth, first_sample, sample_count, sample_stride, capi.RENDER_CLEAR, 0)
+    def render_window(self, width, height, max_depth, first_sample, sample_count, x0, y0, w, h, sample_stride=1, step=1, counted=False):
+        """w x h pixels (x0 + i * step, y0 + j * step) of a width x height film (full-film seeds): (sum, albedo, normal,
+        test), window-sized.  counted: also run every ray through the imported product BVH (import_cwbvh) and leave the
+        visit counts of that ordered traversal in stats()."""
+        p = capi.RenderParams(width, height, max_depth, first_sample, sample_count, sample_stride,
+                              capi.RENDER_CLEAR | (capi.RENDER_COUNTED if counted else 0), 0)
         acc = np.zeros((h, w, 4), np.float32)
         alb, nrm = np.zeros((h, w, 3), np.float32), np.zeros((h, w, 3), np.float32)
         tst = np.zeros((h, w), np.float32)
         t = capi.RenderTargets(acc.ctypes.data, alb.ctypes.data, nrm.ctypes.data, tst.ctypes.data)
-        self._ck(self.api._render_window(self.h, C.byref(p), C.byref(t), x0, y0, w, h), "render_window")
+        self._ck(self.api._render_window(self.h, C.byref(p), C.byref(t), x0, y0, w, h, step), "render_window")
         return acc, alb, nrm, tst
+
+    def import_cwbvh(self, product_ctx) -> dict:
+        """Export the committed 8-wide BVH of a product context (pb_export_bvh) and import it here; the scene of both
+        contexts must be the same.  Returns sizes (nodes, prims, leaf slots)."""
+        api = product_ctx.api
+        nn, npr = C.c_uint64(), C.c_uint64()
+        product_ctx._ck(api._export_bvh(product_ctx.h, None, C.byref(nn), None, C.byref(npr)), "export_bvh")
+        nodes = np.zeros(max(1, nn.value) * 80, np.uint8)
+        prims = np.zeros(max(1, npr.value) * 12, np.float32)
+        product_ctx._ck(api._export_bvh(product_ctx.h, nodes.ctypes.data, C.byref(nn), prims.ctypes.data, C.byref(npr)), "export_bvh")
+        self._ck(self.api._import_cwbvh(self.h, nodes.ctypes.data, nn.value, prims.ctypes.data, npr.value), "import_cwbvh")
+        return {"n_nodes": nn.value, "n_prims": npr.value, "n_leaf_slots": int(self.api._cwbvh_leaf_slots(self.h))}
+
+    def trace_cwbvh(self, rays, any_hit=False):
+        """Ordered, t-culled traversal of the imported BVH: (hits | occluded, {nodes, tris, spheres})."""
+        rays = np.ascontiguousarray(rays, capi.RAY_DTYPE)
+        out = np.empty(rays.shape[0], np.uint8 if any_hit else capi.HIT_DTYPE)
+        cnt = (C.c_uint64 * 3)()
+        self._ck(self.api._trace_cwbvh(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data, int(any_hit), cnt), "trace_cwbvh")
+        return out, {"nodes": int(cnt[0]), "tris": int(cnt[1]), "spheres": int(cnt[2])}
 
     def rng_stream(self, v0: int, v1: int, n: int):
         seed = C.c_uint32()

@@ -154,6 +154,12 @@ void hs_trace_any(HS* h, const float* rays, uint64_t n, uint8_t* occ) {
         occ[i] = hit.prim != 0xFFFFFFFFu;
     }
 }
+// the committed tree as pb_export_bvh hands it out: 80-byte nodes + 48-byte primitive records in leaf order
+void hs_export(HS* h, void* nodes80, void* prims48) {
+    if (nodes80 && !h->nodes.empty()) memcpy(nodes80, h->nodes.data(), h->nodes.size() * sizeof(Node8));
+    if (prims48 && !h->prims_out.empty()) memcpy(prims48, h->prims_out.data(), h->prims_out.size() * sizeof(PrimRec));
+}
+uint32_t hs_num_prims(HS* h) { return (uint32_t)h->prims_out.size(); }
 // per-BSDF known-answer table computed by the product's pb_bsdf.cuh on the CPU (tests/devsim/table_body.h)
 int hs_bsdf_table(const pb_material* mat, const float* wo, const uint32_t* seeds, uint32_t n, float* out) {
     if (!mat) return 1;
