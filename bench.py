@@ -170,8 +170,9 @@ def build_scene(ctx, mesh_tag: str, mesh=None):
 
 
 # --------------------------------------------------------------------------------------------------
-def cpu_leg(mesh_tag, mesh, seconds_target, steps, warmup, want_line):
-    """The reference integrator's header code on the host cores (oracle/_ref), bounded sample."""
+def cpu_leg(mesh_tag, mesh, seconds_target, steps, warmup, want_line, keep=None):
+    """The reference integrator's header code on the host cores (oracle/_ref), bounded sample.  `keep` (a dict) receives
+    the oracle context with the scene built, for the roofline's visit-count pass."""
     from oracle import pyoracle
     api = pyoracle.load()
     o = pyoracle.OracleContext(api)
@@ -185,6 +186,8 @@ def cpu_leg(mesh_tag, mesh, seconds_target, steps, warmup, want_line):
         api._set_threads(avail)
     cores = int(api._max_threads())
     info, mesh = build_scene(o, mesh_tag, mesh)
+    if keep is not None:
+        keep["oracle"] = o
     # probe, then the largest film (same camera, same scene) whose 1-spp frame fits the time budget
     t0 = time.time(); o.render(240, 135, MAX_DEPTH, 0, 1, want_aov=False); probe = 240 * 135 / (time.time() - t0)
     film = (240, 135)
@@ -326,6 +329,23 @@ def product_main(args):
     value = samples / (ms * 1e-3) / 1e6
     mrays = (rays_c_all + rays_a_all) / (ms * 1e-3) / 1e6
 
+    # ---- the same K steps on the shipped launch path (one CUDA graph per wave; the region above launches kernel by
+    # kernel because it records events around every traversal launch for the roofline)
+    barrier()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dev_step(args.warmup, timing=False)          # captures the graph outside the timed region
+    barrier()
+    g0.record(stream)
+    for i in range(args.steps):
+        dev_step(args.warmup + i, timing=False, asynchronous=True)
+    g1.record(stream)
+    barrier()
+    g.stats()
+    graph_ms = g0.elapsed_time(g1)
+    if N > 1:
+        tg = torch.tensor([graph_ms], dtype=torch.float64, device=dev); dist.all_reduce(tg, op=dist.ReduceOp.MAX); graph_ms = float(tg[0])
+    graph_value = samples / (graph_ms * 1e-3) / 1e6
+
     # ---- e2e: the same steps through the C ABI with HOST buffers (pinned), copies inside the call
     h_sum = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32).pin_memory()
     h_ptr = h_sum.data_ptr()
@@ -374,7 +394,21 @@ def product_main(args):
     h2d = n_px * 16 + C.sizeof(capi.RenderParams)
     d2h = n_px * 16
 
-    # ---- roofline of the dominant kernel (k_extend): algorithmic bytes from a counted pass (untimed)
+    # ---- CPU baseline (rank 0, N = 1 only): the oracle on the host cores, bounded sample
+    cpu = None
+    kept = {}
+    if rank == 0 and N == 1 and not args.no_cpu:
+        try:
+            cpu, _, _ = cpu_leg(args.mesh, mesh, 10.0, 2, 1, False, keep=kept)
+        except Exception as e:  # the baseline is a report, never a reason to lose the GPU line
+            cpu = {"value": None, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
+
+    # ---- roofline of the dominant kernel (k_extend).  Algorithmic bytes per ray = 48 + 80 n_nodes + 48 n_tri
+    # + 32 n_sph with the visit counts of the ORACLE's ordered, t-culled traversal of the BVH this context committed
+    # (pb_export_bvh -> oracle/orc_cwbvh.h), taken over the rays of a strided sample of the first timed step's first frame
+    # (every 8th pixel in x and y, the oracle's own path tracer generates the rays: same seeds, same paths).  The kernel's
+    # own visit counters (PB_RENDER_COUNTED: octant order, batched primitive tests, stale stack entries) are reported next
+    # to it and are only the fallback when the oracle leg is switched off (--no-cpu).
     roof = None
     extra = {}
     if rank == 0:
@@ -385,23 +419,67 @@ def product_main(args):
         b_closest = 48.0 + (80.0 * sc["node_visits"] + 48.0 * sc["prim_tests_tri"] + 32.0 * sc["prim_tests_sphere"]) / rc
         b_any = 33.0 + (80.0 * sc["node_visits_any"] + 48.0 * sc["prim_tests_tri_any"] + 32.0 * sc["prim_tests_sphere_any"]) / ra
         peak, peak_src = peaks()
+        kernel_counters = {"bytes_per_ray": b_closest, "nodes_per_ray": sc["node_visits"] / rc, "tris_per_ray": sc["prim_tests_tri"] / rc,
+                           "spheres_per_ray": sc["prim_tests_sphere"] / rc, "bytes_per_ray_any": b_any,
+                           "source": "PB_RENDER_COUNTED pass over the first timed step's frames (the kernel's own counters)"}
+        bytes_from = kernel_counters["source"] + " — oracle leg off"
+        b_min = None
+        oc = None
+        o = kept.get("oracle")
+        if o is not None:
+            try:
+                t_o = time.time()
+                o.set_backend(0)
+                bvh = o.import_cwbvh(g)
+                step = 8
+                o.render_window(WIDTH, HEIGHT, MAX_DEPTH, args.warmup * S * N, 1, 0, 0, (WIDTH + step - 1) // step, (HEIGHT + step - 1) // step,
+                                step=step, counted=True)
+                so = o.stats()
+                orc, ora = max(1, so["rays_closest"]), max(1, so["rays_any"])
+                oc = {"nodes_per_ray": so["node_visits"] / orc, "tris_per_ray": so["prim_tests_tri"] / orc, "spheres_per_ray": so["prim_tests_sphere"] / orc,
+                      "rays": so["rays_closest"], "nodes_per_ray_any": so["node_visits_any"] / ora, "rays_any": so["rays_any"]}
+                b_closest = 48.0 + (80.0 * so["node_visits"] + 48.0 * so["prim_tests_tri"] + 32.0 * so["prim_tests_sphere"]) / orc
+                b_any = 33.0 + (80.0 * so["node_visits_any"] + 48.0 * so["prim_tests_tri_any"] + 32.0 * so["prim_tests_sphere_any"]) / ora
+                bytes_from = (f"oracle's ordered, t-culled traversal of the exported BVH (oracle/orc_cwbvh.h) over the {so['rays_closest']} closest-hit rays of "
+                              f"every {step}th pixel in x and y of frame {args.warmup * S * N}, depth {MAX_DEPTH} ({time.time() - t_o:.1f} s)")
+                import math
+                levels = max(1, math.ceil(math.log(max(2, bvh["n_leaf_slots"]), 8)))
+                per_leaf = bvh["n_prims"] / max(1, bvh["n_leaf_slots"])
+                b_min = {"bytes_per_ray": 48.0 + 80.0 * levels + 48.0 * per_leaf, "levels": levels, "prims_per_leaf_slot": per_leaf,
+                         "n_leaf_slots": bvh["n_leaf_slots"], "formula": "48 + 80 ceil(log8(leaf slots)) + 48 prims per leaf slot (SURVEY 8d)"}
+            except Exception as e:
+                bytes_from = kernel_counters["source"] + f" — oracle leg failed: {e}"
         ach = rays_c * b_closest / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
         ach_any = rays_a * b_any / (con_ms * 1e-3) / 1e9 if con_ms > 0 else 0.0
         traffic = None
+        prof = {}
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get("k_extend_dram_bytes_per_launch")
+                prof = json.load(open(tp))
+                traffic = prof.get("k_extend_dram_bytes_per_launch")
             except Exception:
                 traffic = None
         roof = {"bound": "hbm", "kernel": "k_extend (closest-hit traversal of the 8-wide BVH)", "achieved": ach, "peak": peak,
                 "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_ray": b_closest, "bytes_per_launch": rays_c * b_closest / max(1, ext_l),
                 "avg_launch_ms": ext_ms / max(1, ext_l), "launches": ext_l,
-                "nodes_per_ray": sc["node_visits"] / rc, "tris_per_ray": sc["prim_tests_tri"] / rc,
-                "spheres_per_ray": sc["prim_tests_sphere"] / rc,
+                "nodes_per_ray": (oc or kernel_counters)["nodes_per_ray"], "tris_per_ray": (oc or kernel_counters)["tris_per_ray"],
+                "spheres_per_ray": (oc or kernel_counters)["spheres_per_ray"],
                 "share_of_step": ext_ms / ms if N == 1 else None,
-                "bytes_from": "counted pass over the first timed step's frames (PB_RENDER_COUNTED), scaled by each step's ray count"}
+                "bytes_from": bytes_from, "oracle_counts": oc, "kernel_counters": kernel_counters}
+        avg_s = ext_ms * 1e-3 / max(1, ext_l)
+        if b_min:      # the implementation-independent floor of SURVEY 8(d)
+            roof["b_min"] = b_min
+            roof["b_min_frac"] = rays_c * b_min["bytes_per_ray"] / (ext_ms * 1e-3) / 1e9 / peak if ext_ms > 0 else None
+        if traffic and avg_s > 0:   # what really crosses the HBM pins (ncu dram__bytes of profiles/, per launch)
+            roof["dram_frac"] = traffic / avg_s / 1e9 / peak
+            roof["traffic_source"] = prof.get("source")
+        wi = prof.get("k_extend_warp_inst_per_ray")
+        if wi and ext_ms > 0 and clk and clk.get("sm_mhz"):
+            slots = 148 * 4 * clk["sm_mhz"] * 1e6     # warp instructions the SM sub-partitions can issue per second
+            roof["issue"] = {"warp_inst_per_ray": wi, "issue_slots_per_s": slots, "frac": wi * rays_c / (ext_ms * 1e-3) / slots,
+                             "note": "the binding ceiling: ncu smsp__inst_executed per ray (profiles/) x rays / time / (148 SMs x 4 x SM clock)"}
         extra["roofline_connect"] = {"bound": "hbm", "kernel": "k_connect (any-hit traversal)", "achieved": ach_any, "peak": peak,
                                      "unit": "GB/s", "frac": ach_any / peak, "bytes_per_ray": b_any,
                                      "avg_launch_ms": con_ms / max(1, con_l), "launches": con_l,
@@ -412,14 +490,6 @@ def product_main(args):
         extra["shade_share_of_step"] = shd_ms / ms if N == 1 else None
         extra["mrays_per_s_closest_kernel"] = rays_c / (ext_ms * 1e-3) / 1e6 if ext_ms > 0 else None
         extra["mrays_per_s_any_kernel"] = rays_a / (con_ms * 1e-3) / 1e6 if con_ms > 0 else None
-
-    # ---- CPU baseline (rank 0, N = 1 only): the oracle on the host cores, bounded sample
-    cpu = None
-    if rank == 0 and N == 1 and not args.no_cpu:
-        try:
-            cpu, _, _ = cpu_leg(args.mesh, mesh, 10.0, 2, 1, False)
-        except Exception as e:  # the baseline is a report, never a reason to lose the GPU line
-            cpu = {"value": None, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {e}"}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "Msamples/s", "n_gpus": N, "steps": args.steps,
@@ -432,6 +502,10 @@ def product_main(args):
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "api": "pb_render(PB_RENDER_HOST_BUFFERS | PB_RENDER_ASYNC) x steps + pb_wait", "host_enqueue_ms_each": e2e_async_host,
                         "sync": {"value": sync_value, "ms_per_step": sync_ms / e2e_steps, "ms_each": e2e_each, "api": "pb_render(PB_RENDER_HOST_BUFFERS), one synchronous call per step"}},
+                "launch_path": {"value": "kernel by kernel (PB_RENDER_STAGE_TIMING: CUDA events around every traversal launch feed the roofline)",
+                                "graph": {"value": graph_value, "ms_per_step": graph_ms / args.steps,
+                                          "note": "the same steps on the shipped default path: one CUDA graph launch per wave"},
+                                "e2e": "graph"},
                 "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
                 "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}
         line.update(extra)

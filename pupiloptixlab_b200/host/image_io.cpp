@@ -12,6 +12,11 @@
 namespace pupil::host {
 namespace {
 
+// Untrusted headers: every decoder bounds its dimensions before it multiplies or allocates (no size_t overflow, no
+// multi-gigabyte allocation for a 30-byte file).  2^15 x 2^15 texels covers any texture or environment map.
+bool dims_ok(long long w, long long h) { return w > 0 && h > 0 && w <= 32768 && h <= 32768; }
+
+
 struct Bytes {            // decoded 8-bit image, `c` interleaved channels (1 grey, 2 grey+alpha, 3 rgb, 4 rgba)
     int w = 0, h = 0, c = 0;
     std::vector<unsigned char> px;
@@ -143,15 +148,19 @@ bool read_png(const unsigned char* d, size_t n, Bytes& out, std::string& err) {
 }
 
 // ---- BMP (BITMAPINFOHEADER family, uncompressed 8 / 24 / 32 bit) ---------------------------------------------------
+
 bool read_bmp(const unsigned char* d, size_t n, Bytes& out, std::string& err) {
     if (n < 54 || d[0] != 'B' || d[1] != 'M') { err = "bmp: bad header"; return false; }
     const uint32_t data_off = le32(d + 10), hdr = le32(d + 14);
     const int32_t W = (int32_t)le32(d + 18), Hs = (int32_t)le32(d + 22);
     const uint32_t bpp = le16(d + 28), comp = le32(d + 30);
-    if (hdr < 40 || W <= 0 || Hs == 0 || !(comp == 0 || comp == 3) || !(bpp == 8 || bpp == 24 || bpp == 32)) { err = "bmp: unsupported variant"; return false; }
+    if (hdr < 40 || Hs == INT32_MIN || !(comp == 0 || comp == 3) || !(bpp == 8 || bpp == 24 || bpp == 32)) { err = "bmp: unsupported variant"; return false; }
     const int H = Hs < 0 ? -Hs : Hs;
+    if (!dims_ok(W, H)) { err = "bmp: bad dimensions"; return false; }
     const size_t stride = ((size_t)W * bpp / 8 + 3) & ~(size_t)3;
-    if (data_off + stride * H > n) { err = "bmp: truncated"; return false; }
+    if ((size_t)data_off > n || stride * (size_t)H > n - data_off) { err = "bmp: truncated"; return false; }
+    // 8-bit files index a 256-entry BGRA palette right behind the info header: all of it must be inside the file
+    if (bpp == 8 && ((size_t)hdr > n || 14 + (size_t)hdr + 4 * 256 > n)) { err = "bmp: palette outside the file"; return false; }
     const unsigned char* pal = d + 14 + hdr;
     out.w = W; out.h = H; out.c = bpp == 32 ? 4 : 3;
     out.px.resize((size_t)W * H * out.c);
@@ -170,7 +179,7 @@ bool read_bmp(const unsigned char* d, size_t n, Bytes& out, std::string& err) {
 bool read_tga(const unsigned char* d, size_t n, Bytes& out, std::string& err) {
     if (n < 18) { err = "tga: truncated"; return false; }
     const int id_len = d[0], cmap = d[1], type = d[2], W = (int)le16(d + 12), H = (int)le16(d + 14), bpp = d[16], desc = d[17];
-    if (cmap || !(type == 2 || type == 3 || type == 10 || type == 11) || W <= 0 || H <= 0 || !(bpp == 8 || bpp == 24 || bpp == 32)) { err = "tga: unsupported variant"; return false; }
+    if (cmap || !(type == 2 || type == 3 || type == 10 || type == 11) || !dims_ok(W, H) || !(bpp == 8 || bpp == 24 || bpp == 32)) { err = "tga: unsupported variant"; return false; }
     const int bytes = bpp / 8;
     out.w = W; out.h = H; out.c = bytes == 1 ? 1 : bytes;
     out.px.resize((size_t)W * H * out.c);
@@ -216,16 +225,16 @@ bool pnm_token(const unsigned char* d, size_t n, size_t& pos, long& v) {
     }
     if (pos >= n || !isdigit(d[pos])) return false;
     v = 0;
-    while (pos < n && isdigit(d[pos])) v = v * 10 + (d[pos++] - '0');
+    while (pos < n && isdigit(d[pos])) { v = v * 10 + (d[pos++] - '0'); if (v > 100000000L) return false; }   // no signed overflow on digit runs
     return true;
 }
 bool read_pnm(const unsigned char* d, size_t n, Bytes& out, std::string& err) {
     const int c = d[1] == '5' ? 1 : 3;
     size_t pos = 2;
     long W, H, mx;
-    if (!pnm_token(d, n, pos, W) || !pnm_token(d, n, pos, H) || !pnm_token(d, n, pos, mx) || mx <= 0 || mx > 255 || W <= 0 || H <= 0) { err = "pnm: bad header"; return false; }
+    if (!pnm_token(d, n, pos, W) || !pnm_token(d, n, pos, H) || !pnm_token(d, n, pos, mx) || mx <= 0 || mx > 255 || !dims_ok(W, H)) { err = "pnm: bad header"; return false; }
     ++pos;   // the single whitespace after maxval
-    if (pos + (size_t)W * H * c > n) { err = "pnm: truncated"; return false; }
+    if (pos > n || (size_t)W * H * c > n - pos) { err = "pnm: truncated"; return false; }
     out.w = (int)W; out.h = (int)H; out.c = c;
     out.px.assign(d + pos, d + pos + (size_t)W * H * c);
     if (mx != 255) for (auto& v : out.px) v = (unsigned char)((int)v * 255 / mx);
@@ -257,7 +266,7 @@ bool read_hdr(const unsigned char* d, size_t n, Image& out, std::string& err) {
     if (!fmt) { err = "hdr: unsupported format"; return false; }
     line(l);
     int W = 0, H = 0;
-    if (sscanf(l.c_str(), "-Y %d +X %d", &H, &W) != 2 || W <= 0 || H <= 0) { err = "hdr: unsupported orientation"; return false; }
+    if (sscanf(l.c_str(), "-Y %d +X %d", &H, &W) != 2 || !dims_ok(W, H)) { err = "hdr: unsupported orientation"; return false; }
     out.w = W; out.h = H;
     out.rgba.resize((size_t)W * H * 4);
     std::vector<unsigned char> scan((size_t)W * 4);
@@ -300,12 +309,18 @@ bool read_hdr(const unsigned char* d, size_t n, Image& out, std::string& err) {
 
 // ---- PFM ("PF" colour / "Pf" grey, little or big endian, bottom row first) -------------------------------------------
 bool read_pfm(const unsigned char* d, size_t n, Image& out, std::string& err) {
+    if (n < 3) { err = "pfm: truncated"; return false; }
     const int c = d[1] == 'F' ? 3 : 1;
     int W = 0, H = 0, used = 0;
     float scale = 0.f;
-    if (sscanf((const char*)d + 2, "%d %d %f%n", &W, &H, &scale, &used) != 3 || W <= 0 || H <= 0) { err = "pfm: bad header"; return false; }
+    // the header is text inside a binary file that is not NUL-terminated: parse a bounded, terminated copy of it
+    char head[96];
+    const size_t hn = std::min(n - 2, sizeof head - 1);
+    memcpy(head, d + 2, hn);
+    head[hn] = 0;
+    if (sscanf(head, "%d %d %f%n", &W, &H, &scale, &used) != 3 || !dims_ok(W, H)) { err = "pfm: bad header"; return false; }
     size_t pos = 2 + (size_t)used + 1;
-    if (pos + (size_t)W * H * c * 4 > n) { err = "pfm: truncated"; return false; }
+    if (pos > n || (size_t)W * H * c * 4 > n - pos) { err = "pfm: truncated"; return false; }
     const bool little = scale < 0.f;
     out.w = W; out.h = H;
     out.rgba.resize((size_t)W * H * 4);
@@ -356,7 +371,7 @@ bool read_exr(const unsigned char* d, size_t n, Image& out, std::string& err) {
         if (pos + 4 > n) { err = "exr: truncated header"; return false; }
         const uint32_t size = le32(d + pos);
         pos += 4;
-        if (pos + size > n) { err = "exr: truncated header"; return false; }
+        if ((size_t)size > n - pos) { err = "exr: truncated header"; return false; }
         const unsigned char* v = d + pos;
         if (name == "channels") {
             size_t q = 0;
@@ -370,14 +385,15 @@ bool read_exr(const unsigned char* d, size_t n, Image& out, std::string& err) {
                 q += 16;
                 chans.push_back(c);
             }
-        } else if (name == "compression") comp = v[0];
+        } else if (name == "compression" && size >= 1) comp = v[0];
         else if (name == "dataWindow" && size >= 16) { x0 = (int)le32(v); y0 = (int)le32(v + 4); x1 = (int)le32(v + 8); y1 = (int)le32(v + 12); }
         pos += size;
     }
     if (chans.empty() || x1 < x0 || y1 < y0) { err = "exr: missing channels / dataWindow"; return false; }
     if (!(comp == 0 || comp == 2 || comp == 3)) { err = "exr: only NONE / ZIPS / ZIP compression is supported"; return false; }
+    if (!dims_ok((long long)x1 - x0 + 1, (long long)y1 - y0 + 1) || chans.size() > 64) { err = "exr: bad dataWindow / channel count"; return false; }
     const int W = x1 - x0 + 1, H = y1 - y0 + 1, lines = comp == 3 ? 16 : 1, n_chunks = (H + lines - 1) / lines;
-    if (pos + (size_t)n_chunks * 8 > n) { err = "exr: truncated offset table"; return false; }
+    if (pos > n || (size_t)n_chunks * 8 > n - pos) { err = "exr: truncated offset table"; return false; }
     size_t line_bytes = 0;
     std::vector<size_t> ch_off(chans.size());
     for (size_t c = 0; c < chans.size(); ++c) { ch_off[c] = line_bytes; line_bytes += (size_t)W * (chans[c].type == 1 ? 2 : 4); }
@@ -397,10 +413,11 @@ bool read_exr(const unsigned char* d, size_t n, Image& out, std::string& err) {
     std::vector<unsigned char> raw, tmp;
     for (int k = 0; k < n_chunks; ++k) {
         uint64_t off = (uint64_t)le32(d + pos + 8 * (size_t)k) | (uint64_t)le32(d + pos + 8 * (size_t)k + 4) << 32;
-        if (off + 8 > n) { err = "exr: bad chunk offset"; return false; }
-        const int y = (int)le32(d + off) - y0;
+        if (off > n || n - off < 8) { err = "exr: bad chunk offset"; return false; }
+        const long long yl = (long long)(int)le32(d + off) - y0;
         const uint32_t sz = le32(d + off + 4);
-        if (off + 8 + sz > n || y < 0 || y >= H) { err = "exr: bad chunk"; return false; }
+        if ((uint64_t)sz > n - off - 8 || yl < 0 || yl >= H) { err = "exr: bad chunk"; return false; }
+        const int y = (int)yl;
         const int rows = std::min(lines, H - y);
         const size_t want = line_bytes * rows;
         const unsigned char* src = d + off + 8;

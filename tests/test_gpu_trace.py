@@ -75,3 +75,41 @@ def test_mesh_1m_coherent_and_incoherent(api, oracle_api):
     assert np.array_equal(g.trace_any(r2), o.trace_any(r2))
     st = g.stats()
     assert st["n_prims"] == info["n_tris"] + 1000 + 2
+
+
+def test_counted_traversal_against_oracle_counts(api, oracle_api):
+    """B_ray comes from the ORACLE's ordered, t-culled traversal of the committed BVH (pb_export_bvh ->
+    oracle/orc_cwbvh.h).  The export passes the oracle's structural checks, the oracle's traversal of the product's tree
+    returns the product's hits bit for bit, and the kernel's own counters (PB_*_COUNTED: octant order, batched primitive
+    tests, stale stack entries) are compared with the oracle's: the kernel never visits fewer nodes than the ordered
+    traversal, and the excess stays bounded (the bench reports both; roofline.achieved uses the oracle's)."""
+    n = scenes.MESH_N["1M"]
+    mesh = scenes.displaced_mesh(n)
+    o = pyoracle.OracleContext(oracle_api)
+    g = capi.Context(api)
+    for ctx in (o, g):
+        scenes.bench_scene(ctx, n, 2000, 1920, 1080, patchwork=True, mesh=mesh)
+    info = o.import_cwbvh(g)
+    assert info["n_prims"] == g.stats()["n_prims"] and info["n_nodes"] == g.stats()["n_nodes"] and info["n_leaf_slots"] > 0
+    fov_y = scenes.fov_x_to_y(45.0, 1920, 1080)
+    s2c = scenes.perspective_sample_to_camera(fov_y, np.float32(1920) / np.float32(1080))
+    c2w = scenes.sensor_to_world(scenes.lookat_to_world(**{k: scenes.BENCH_CAMERA[k] for k in ("origin", "target", "up")}))
+    px = np.random.RandomState(8).randint(0, 1920 * 1080, 100000).astype(np.uint32)
+    cam = scenes.camera_rays(s2c, c2w, 1920, 1080, 0, px)
+    h0 = g.trace_closest(cam)
+    hit = h0["prim"] != capi.MISS
+    p = np.stack([cam[k][hit] + h0["t"][hit] * cam[d][hit] for k, d in (("ox", "dx"), ("oy", "dy"), ("oz", "dz"))], -1)
+    bounce = U.random_rays(len(p), 12)
+    bounce["ox"], bounce["oy"], bounce["oz"] = p.T.astype(np.float32)
+    for name, rays in (("camera", cam), ("bounce", bounce)):
+        want, oc = o.trace_cwbvh(rays)
+        got = g.trace_closest(rays, counted=True)
+        st = g.stats()
+        _cmp(got, want)
+        kc = {"nodes": st["node_visits"], "tris": st["prim_tests_tri"], "spheres": st["prim_tests_sphere"]}
+        alg = lambda c: 48.0 + (80 * c["nodes"] + 48 * c["tris"] + 32 * c["spheres"]) / len(rays)
+        print(f"{name}: oracle ordered traversal {oc} = {alg(oc):.0f} B/ray; kernel counters {kc} = {alg(kc):.0f} B/ray")
+        assert oc["nodes"] <= kc["nodes"] <= 2.0 * oc["nodes"]
+        assert alg(oc) <= alg(kc) * 1.02 and alg(kc) <= 2.0 * alg(oc)
+        occ, oa = o.trace_cwbvh(rays, any_hit=True)
+        assert np.array_equal(g.trace_any(rays, counted=True) != 0, occ != 0)
