@@ -254,6 +254,14 @@ def product_main(args):
         clocks = ClockSampler(local, uuid)
     api = capi.load()
     g = capi.Context(api, local)
+    if N > 1:
+        # the library's own communicator: rank 0's NCCL unique id travels over the process group, every rank joins;
+        # from here on the per-step reduce is the ncclReduce pb_render enqueues itself (PB_RENDER_REDUCE)
+        uid = torch.zeros(128, dtype=torch.uint8, device=torch.device("cuda", local))
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(g.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, src=0)
+        g.comm_init_rank(bytes(uid.cpu().numpy().tobytes()), N, rank)
     info, mesh = build_scene(g, args.mesh)
     st0 = g.stats()
     if rank == 0:
@@ -272,11 +280,13 @@ def product_main(args):
     def step_params(i, flags):
         return capi.RenderParams(WIDTH, HEIGHT, MAX_DEPTH, i * S * N + rank, S, N, flags, 0)
 
+    REDUCE = capi.RENDER_REDUCE if N > 1 else 0
+
     def dev_step(i, timing=True, asynchronous=False):
-        p = step_params(i, capi.RENDER_CLEAR | (capi.RENDER_STAGE_TIMING if timing else 0) | (capi.RENDER_ASYNC if asynchronous else 0))
+        # N > 1: pb_render sums this rank's frames, enqueues ONE ncclReduce(sum, fp32, root 0) behind its last wave on
+        # the same stream and, on rank 0, leaves the reduced film of the step in d_sum
+        p = step_params(i, capi.RENDER_CLEAR | REDUCE | (capi.RENDER_STAGE_TIMING if timing else 0) | (capi.RENDER_ASYNC if asynchronous else 0))
         g.render_dev(p, d_sum.data_ptr(), 0, 0, sp)
-        if N > 1:
-            dist.reduce(d_sum, dst=0)
         if rank == 0:
             d_total.add_(d_sum)
         return None if asynchronous else g.stats()
@@ -351,14 +361,10 @@ def product_main(args):
     h_ptr = h_sum.data_ptr()
 
     def e2e_step(i, asynchronous):
-        # accumulate into the caller's host buffer: upload of the running sums + download of the new ones
-        p = step_params(i, capi.RENDER_HOST_BUFFERS | (capi.RENDER_CLEAR if N > 1 else 0) | (capi.RENDER_ASYNC if asynchronous else 0))
+        # accumulate into the caller's host buffer: upload of the running sums + download of the new ones (with N > 1 on
+        # rank 0 only: the other ranks' frames arrive through the library's ncclReduce, their host buffers are not touched)
+        p = step_params(i, capi.RENDER_HOST_BUFFERS | REDUCE | (capi.RENDER_ASYNC if asynchronous else 0))
         g.render_dev(p, h_ptr, 0, 0, sp)
-        if N > 1:   # per-rank host result -> device -> NCCL reduce -> host on rank 0
-            d_sum.copy_(h_sum, non_blocking=True)
-            dist.reduce(d_sum, dst=0)
-            if rank == 0:
-                h_sum.copy_(d_sum, non_blocking=True)
         if not asynchronous:
             torch.cuda.synchronize(dev)
 
@@ -393,6 +399,27 @@ def product_main(args):
     sync_value = float(n_px) * S * e2e_steps * N / (sync_ms * 1e-3) / 1e6
     h2d = n_px * 16 + C.sizeof(capi.RenderParams)
     d2h = n_px * 16
+
+    # ---- N > 1: does the sharded, NCCL-reduced film equal the film one GPU renders for the same frames?  One more step
+    # on all ranks (library reduce), then rank 0 alone renders the N * S frames of that step itself and compares.
+    parity = None
+    if N > 1:
+        i_chk = args.warmup
+        dev_step(i_chk, timing=False)
+        barrier()
+        if rank == 0:
+            d_one = torch.zeros_like(d_sum)
+            g.render_dev(capi.RenderParams(WIDTH, HEIGHT, MAX_DEPTH, i_chk * S * N, S * N, 1, capi.RENDER_CLEAR, 0), d_one.data_ptr(), 0, 0, sp)
+            torch.cuda.synchronize(dev)
+            a, b = d_sum[..., :3].double(), d_one[..., :3].double()
+            rel = ((a - b).abs() / (b.abs() + 1e-3)).amax(-1)
+            parity = {"frames": S * N, "step": i_chk, "against": "the same frames rendered by rank 0 alone (sample_stride 1)",
+                      "counts_equal": bool(torch.equal(d_sum[..., 3], d_one[..., 3])) and float(d_one[0, 0, 3]) == S * N,
+                      "max_rel": float(rel.max()), "pixels_within_1e-5": float((rel <= 1e-5).double().mean()),
+                      "film_mean_ratio": float(a.mean() / b.mean()),
+                      "note": "frames are bit-identical on every GPU; the only difference is the order of the float additions (per-rank sums, then the reduce)"}
+            del d_one
+        barrier()
 
     # ---- CPU baseline (rank 0, N = 1 only): the oracle on the host cores, bounded sample
     cpu = None
@@ -496,7 +523,7 @@ def product_main(args):
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "mesh": args.mesh, "n_tris": info["n_tris"], "n_spheres": info["n_spheres"],
-                           "spp_per_step": S, "frames_per_gpu_per_step": S, "sharding": f"sample-interleaved x{N} + NCCL reduce" if N > 1 else "none",
+                           "spp_per_step": S, "frames_per_gpu_per_step": S, "sharding": f"sample-interleaved x{N} + one ncclReduce(sum, fp32, root 0) per step issued by pb_render (PB_RENDER_REDUCE)" if N > 1 else "none",
                            "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"},
                 "mrays_per_s": mrays, "rays_per_sample": (rays_c_all + rays_a_all) / samples,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -506,6 +533,7 @@ def product_main(args):
                                 "graph": {"value": graph_value, "ms_per_step": graph_ms / args.steps,
                                           "note": "the same steps on the shipped default path: one CUDA graph launch per wave"},
                                 "e2e": "graph"},
+                "parity_check": parity,
                 "gpu_launches": int(launches_all), "roofline": roof, "cpu_baseline": cpu, "clocks": clk,
                 "bvh_build_ms": st0["build_ms"], "bvh_nodes": st0["n_nodes"]}
         line.update(extra)

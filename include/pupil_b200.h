@@ -31,7 +31,8 @@ enum {
     PB_ERR_CUDA = 2,      /* a CUDA runtime call failed (see pb_last_error)    */
     PB_ERR_NO_DEVICE = 3, /* no CUDA device: there is NO CPU fallback          */
     PB_ERR_LIMIT = 4,     /* a structural limit was exceeded (BVH depth, ...)  */
-    PB_ERR_NOT_COMMITTED = 5
+    PB_ERR_NOT_COMMITTED = 5,
+    PB_ERR_NCCL = 6       /* NCCL missing, a collective failed, or an asynchronous communicator error was polled */
 };
 
 /* ---- textures: mirror of Pupil::util::Texture / cuda::Texture -------------------------------
@@ -118,6 +119,14 @@ enum {
                                     (same image; never the timed build)                          */
     PB_RENDER_STAGE_TIMING = 8u, /* CUDA events around every extend / connect launch: fills
                                     extend_ms / connect_ms / *_launches of pb_stats               */
+    PB_RENDER_REDUCE = 32u,      /* multi-GPU (a communicator is attached, pb_comm_init_rank / pb_create_multi): this rank's
+                                    frames are summed into a context-owned film, ONE ncclReduce(sum, fp32, root 0) of
+                                    w*h*4 floats is enqueued on the same stream behind the last wave, and the ROOT adds
+                                    the reduced film to its accum_sum_rgba (PB_RENDER_CLEAR: replaces it).  Collective:
+                                    every rank calls pb_render with the same film size; the accumulation buffers of the
+                                    other ranks are not written.  The reference is single-GPU (cuda/context.cpp:15-44);
+                                    the sharding is SURVEY 8(e): rank r renders frames first_sample + k * sample_stride
+                                    with first_sample = base + r, sample_stride = n_ranks                              */
     PB_RENDER_ASYNC = 16u        /* return once the work is enqueued on the stream (the reference's
                                     optixLaunch is asynchronous too, pass.h:79-86); pb_wait /
                                     pb_get_stats synchronise and report the totals of all renders
@@ -219,6 +228,30 @@ PB_API int pb_tonemap(pb_ctx* ctx, const float* frame_rgba, uint8_t* rgba8, uint
 PB_API int pb_wait(pb_ctx* ctx);
 /* implies pb_wait */
 PB_API int pb_get_stats(pb_ctx* ctx, pb_stats* out);
+
+/* ---- multi-GPU: one context per GPU, scene + BVH replicated (every context gets the same pb_add_* / pb_scene_commit
+ * calls and builds the identical tree: deterministic build, cheaper than broadcasting it), frames sharded by sample
+ * index, one NCCL reduce of the fp32 sum film per pb_render.  NCCL is loaded at run time (libnccl.so.2, the
+ * copy already in the process if there is one); without it these calls return PB_ERR_NCCL and everything else works.
+ *
+ *  one process per GPU (bench.py under torchrun, MPI, ...):
+ *      rank 0: pb_comm_unique_id(id) -> ship the 128 bytes to every rank by any means
+ *      all   : pb_comm_init_rank(ctx, id, n_ranks, rank)                 (collective)
+ *      all   : pb_render(ctx, {first_sample = base + rank, sample_stride = n_ranks, flags |= PB_RENDER_REDUCE}, ...)
+ *  one process, n GPUs (host/b200_pt_pass.cpp):
+ *      pb_create_multi(ctxs, devices, n)  -> n contexts, rank i on devices[i], communicators from ncclCommInitAll
+ *      pb_render_multi(ctxs, n, p, targets_on_ctx0, streams)             p describes the WHOLE job: frames
+ *                                          first_sample + j * stride, j < sample_count, dealt round-robin to the ranks
+ * Asynchronous NCCL errors (a peer died, a link failed) are polled in pb_wait / pb_get_stats / synchronous pb_render
+ * and reported as PB_ERR_NCCL with the NCCL error string in pb_last_error.                                          */
+#define PB_UNIQUE_ID_BYTES 128
+PB_API int pb_comm_unique_id(unsigned char id[PB_UNIQUE_ID_BYTES]);
+PB_API int pb_comm_init_rank(pb_ctx* ctx, const unsigned char id[PB_UNIQUE_ID_BYTES], int n_ranks, int rank);
+PB_API int pb_comm_info(const pb_ctx* ctx, int* n_ranks, int* rank);      /* 1, 0 when no communicator is attached */
+PB_API int pb_comm_destroy(pb_ctx* ctx);                                  /* also done by pb_destroy             */
+PB_API int pb_create_multi(pb_ctx** out, const int* devices, int n);
+PB_API int pb_render_multi(pb_ctx* const* ctxs, int n, const pb_render_params* p, const pb_render_targets* targets_on_ctx0,
+                           void* const* cuda_streams /* n entries or NULL */);
 
 /* ---- BVH export (test / roofline accounting only): the committed 8-wide BVH and its primitive
  * records, host buffers.  Query sizes by passing NULL pointers.                                  */

@@ -78,6 +78,11 @@ PH_API int  ph_run_path_tracer(const char* xml_path, int device, uint32_t frames
  *   ph_session_sample_count frames accumulated since the last restart (sample_cnt, pt_pass.cpp:43,55)           */
 typedef struct ph_session ph_session;
 PH_API int  ph_session_create(const char* xml_path, int device, ph_session** out);
+/* n GPUs of this box behind one pass: scene + BVH replicated, frames of a run dealt round-robin, one NCCL reduce into
+ * devices[0]'s buffers (pb_create_multi / pb_render_multi).  ph_session_set_frames_per_run: frames per System frame
+ * (B200PTPass::frames_per_run; >= n keeps every GPU busy).                                                         */
+PH_API int  ph_session_create_multi(const char* xml_path, const int* devices, int n, ph_session** out);
+PH_API int  ph_session_set_frames_per_run(ph_session* s, uint32_t frames);
 PH_API void ph_session_destroy(ph_session* s);
 PH_API int  ph_session_run(ph_session* s, uint32_t frames);
 PH_API int  ph_session_move_object(ph_session* s, uint32_t index, const float to_world[16]);

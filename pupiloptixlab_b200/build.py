@@ -9,7 +9,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(CSRC, "libpupil_b200.so")
-SOURCES = ["pb_capi.cu", "pb_commit.cu", "pb_entry.cu", "pb_build.cu", "pb_trace.cu", "pb_wavefront.cu"]
+SOURCES = ["pb_capi.cu", "pb_commit.cu", "pb_entry.cu", "pb_build.cu", "pb_trace.cu", "pb_wavefront.cu", "pb_comm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "--extended-lambda", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-Xptxas", "-v"]
 
@@ -43,7 +43,7 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=6) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [nvcc, "-shared", "-ccbin", "/usr/bin/g++", "-o", OUT, *objs]
+    cmd = [nvcc, "-shared", "-ccbin", "/usr/bin/g++", "-o", OUT, *objs, "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
@@ -98,7 +98,29 @@ def build_devsim(force: bool = False) -> str:
     return out
 
 
+def build_cpp_tests(force: bool = False) -> str:
+    """TEST PROGRAM (not product): tests/cpp/test_multi_gpu.cpp -> tests/cpp/test_multi_gpu, a plain C++ host of the two
+    C ABIs (no Python, no torch).  Built here so that the binary travels to the GPU box."""
+    build_host()
+    d = os.path.join(TESTS_DIR, "cpp")
+    out = os.path.join(d, "test_multi_gpu")
+    src = os.path.join(d, "test_multi_gpu.cpp")
+    deps = [src, HOST_OUT, OUT, os.path.join(os.path.dirname(HERE), "include", "pupil_host.h"), os.path.join(os.path.dirname(HERE), "include", "pupil_b200.h")]
+    if not force and _newer(out, deps):
+        return out
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-Wall", "-I", os.path.join(cuda, "include"), src, "-o", out,
+           "-L", HOST_DIR, "-lpupil_host", "-L", CSRC, "-lpupil_b200", "-L", os.path.join(cuda, "lib64"), "-lcudart",
+           "-Wl,-rpath,$ORIGIN/../../pupiloptixlab_b200/host", "-Wl,-rpath,$ORIGIN/../../pupiloptixlab_b200/csrc",
+           "-Wl,-rpath," + os.path.join(cuda, "lib64")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("tests/cpp build failed:\n" + r.stdout + r.stderr)
+    return out
+
+
 if __name__ == "__main__":
     print(build_native(force="--force" in sys.argv, verbose="-v" in sys.argv))
     print(build_host(force="--force" in sys.argv))
     print(build_devsim(force="--force" in sys.argv))
+    print(build_cpp_tests(force="--force" in sys.argv))

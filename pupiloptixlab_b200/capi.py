@@ -20,7 +20,8 @@ TEX_RGB, TEX_BITMAP, TEX_CHECKERBOARD = 0, 1, 2
 MAT_DIFFUSE, MAT_DIELECTRIC, MAT_ROUGH_DIELECTRIC, MAT_CONDUCTOR, MAT_ROUGH_CONDUCTOR, MAT_PLASTIC, MAT_ROUGH_PLASTIC = range(1, 8)
 SHAPE_FLIP_NORMALS, SHAPE_FLIP_TEX_COORDS = 1, 2
 ENV_NONE, ENV_CONSTANT, ENV_MAP = 0, 1, 2
-RENDER_HOST_BUFFERS, RENDER_CLEAR, RENDER_COUNTED, RENDER_STAGE_TIMING, RENDER_ASYNC = 1, 2, 4, 8, 16
+RENDER_HOST_BUFFERS, RENDER_CLEAR, RENDER_COUNTED, RENDER_STAGE_TIMING, RENDER_ASYNC, RENDER_REDUCE = 1, 2, 4, 8, 16, 32
+ERR_NCCL = 6
 MISS = 0xFFFFFFFF
 
 
@@ -352,6 +353,21 @@ class Context:
         self._ck(self.api._tonemap(self.h, a.ctypes.data, out.ctypes.data, a.size // 4, int(tone_mapping), int(gamma_correct), 1, None), "tonemap")
         return out
 
+    # ---- multi-GPU (one process per GPU): NCCL communicator of this context
+    def comm_unique_id(self) -> bytes:
+        buf = (C.c_ubyte * 128)()
+        self._ck(self.api._comm_unique_id(buf), "comm_unique_id")
+        return bytes(buf)
+
+    def comm_init_rank(self, unique_id: bytes, n_ranks: int, rank: int):
+        buf = (C.c_ubyte * 128).from_buffer_copy(unique_id)
+        self._ck(self.api._comm_init_rank(self.h, buf, n_ranks, rank), "comm_init_rank")
+
+    def comm_info(self):
+        n, r = C.c_int(), C.c_int()
+        self._ck(self.api._comm_info(self.h, C.byref(n), C.byref(r)), "comm_info")
+        return n.value, r.value
+
     def wait(self):
         """Synchronises renders enqueued with RENDER_ASYNC."""
         self._ck(self.api._wait(self.h), "wait")
@@ -374,5 +390,11 @@ def load() -> Api:
         api._f("trace_closest_counted", i32, [vp, vp, u64, vp, i32, vp])
         api._f("trace_any_counted", i32, [vp, vp, u64, vp, i32, vp])
         api._f("export_bvh", i32, [vp, vp, C.POINTER(u64), vp, C.POINTER(u64)])
+        api._f("comm_unique_id", i32, [vp])
+        api._f("comm_init_rank", i32, [vp, vp, i32, i32])
+        api._f("comm_info", i32, [vp, C.POINTER(i32), C.POINTER(i32)])
+        api._f("comm_destroy", i32, [vp])
+        api._f("create_multi", i32, [C.POINTER(vp), C.POINTER(i32), i32])
+        api._f("render_multi", i32, [C.POINTER(vp), i32, C.POINTER(RenderParams), C.POINTER(RenderTargets), C.POINTER(vp)])
         _product = api
     return _product

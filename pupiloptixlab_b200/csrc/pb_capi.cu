@@ -56,6 +56,7 @@ PB_API void pb_destroy(pb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     wavefront_free(c);
+    comm_free(c);
     free_device_scene(c);
     cudaFree(c->d_counters);
     cudaFree(c->d_stage);

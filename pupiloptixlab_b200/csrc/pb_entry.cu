@@ -94,7 +94,31 @@ PB_API int pb_render_ex(pb_ctx* c, const pb_render_params* p, const pb_render_ta
     cudaSetDevice(c->device);
     cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
     const size_t npx = (size_t)p->width * p->height;
+    const bool reduce = (p->flags & PB_RENDER_REDUCE) != 0u;
+    if (reduce && !c->nccl_comm) { c->err = "PB_RENDER_REDUCE without a communicator (pb_comm_init_rank / pb_create_multi)"; return PB_ERR_INVALID; }
+    // this rank's frames -> its own cleared film -> ncclReduce to rank 0 on the same stream -> the root adds the result
+    auto render_reduced = [&](float* d_dst, float* d_alb, float* d_nrm, float* d_tst) -> int {
+        int rc = comm_reserve_film(c, npx);
+        if (rc != PB_OK) return rc;
+        pb_render_params q = *p;
+        q.flags = (p->flags & ~(uint32_t)(PB_RENDER_REDUCE | PB_RENDER_HOST_BUFFERS)) | PB_RENDER_CLEAR | PB_RENDER_ASYNC;
+        rc = wavefront_render(c, &q, c->d_reduce, d_alb, d_nrm, d_tst, s);
+        if (rc == PB_OK) rc = comm_reduce_enqueue(c, c->d_reduce, npx, s);
+        if (rc == PB_OK && c->rank == 0) {
+            if (p->flags & PB_RENDER_CLEAR) PB_CUDA_TRY(c, cudaMemcpyAsync(d_dst, c->d_reduce, npx * 16, cudaMemcpyDeviceToDevice, s));
+            else rc = film_add(c, d_dst, c->d_reduce, (uint32_t)npx, s);
+        }
+        return rc;
+    };
+    auto finish = [&](int rc) -> int {     // synchronous calls: wait, then poll the communicator
+        if (p->flags & PB_RENDER_ASYNC) return rc;
+        const int rw = wavefront_wait(c);
+        if (rc == PB_OK) rc = rw;
+        if (rc == PB_OK && reduce) rc = comm_poll(c);
+        return rc;
+    };
     if (!(p->flags & PB_RENDER_HOST_BUFFERS)) {
+        if (reduce) return finish(render_reduced(accum_sum_rgba, albedo_rgb, normal_rgb, test));
         return wavefront_render(c, p, accum_sum_rgba, albedo_rgb, normal_rgb, test, s);   // synchronises unless PB_RENDER_ASYNC
     }
     const auto h0 = std::chrono::steady_clock::now();
@@ -109,12 +133,13 @@ PB_API int pb_render_ex(pb_ctx* c, const pb_render_params* p, const pb_render_ta
     float* d_alb = albedo_rgb ? c->d_stage + npx * 4 : nullptr;
     float* d_nrm = normal_rgb ? c->d_stage + npx * 7 : nullptr;
     float* d_tst = test ? c->d_stage + npx * 10 : nullptr;
-    if (!(p->flags & PB_RENDER_CLEAR)) PB_CUDA_TRY(c, cudaMemcpyAsync(d_sum, accum_sum_rgba, npx * 16, cudaMemcpyHostToDevice, s));
+    const bool owns_sum = !reduce || c->rank == 0;      // with PB_RENDER_REDUCE only the root's accumulation buffer is read / written
+    if (!(p->flags & PB_RENDER_CLEAR) && owns_sum) PB_CUDA_TRY(c, cudaMemcpyAsync(d_sum, accum_sum_rgba, npx * 16, cudaMemcpyHostToDevice, s));
     pb_render_params q = *p;
     q.flags |= PB_RENDER_ASYNC;          // one synchronise for kernels and copies together (wavefront_wait below)
-    int rc = wavefront_render(c, &q, d_sum, d_alb, d_nrm, d_tst, s);
+    int rc = reduce ? render_reduced(d_sum, d_alb, d_nrm, d_tst) : wavefront_render(c, &q, d_sum, d_alb, d_nrm, d_tst, s);
     if (rc == PB_OK) {
-        cudaError_t e = cudaMemcpyAsync(accum_sum_rgba, d_sum, npx * 16, cudaMemcpyDeviceToHost, s);
+        cudaError_t e = owns_sum ? cudaMemcpyAsync(accum_sum_rgba, d_sum, npx * 16, cudaMemcpyDeviceToHost, s) : cudaSuccess;
         if (e == cudaSuccess && albedo_rgb) e = cudaMemcpyAsync(albedo_rgb, d_alb, npx * 12, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && normal_rgb) e = cudaMemcpyAsync(normal_rgb, d_nrm, npx * 12, cudaMemcpyDeviceToHost, s);
         if (e == cudaSuccess && test) e = cudaMemcpyAsync(test, d_tst, npx * 4, cudaMemcpyDeviceToHost, s);
@@ -125,6 +150,7 @@ PB_API int pb_render_ex(pb_ctx* c, const pb_render_params* p, const pb_render_ta
         if (p->flags & PB_RENDER_ASYNC) return rc;
         const int rw = wavefront_wait(c);
         if (rc == PB_OK) rc = rw;
+        if (rc == PB_OK && reduce) rc = comm_poll(c);
         if (getenv("PB_DEBUG_TIMING")) {
             const auto h2 = std::chrono::steady_clock::now();
             auto us = [](auto a, auto b) { return (long)std::chrono::duration_cast<std::chrono::microseconds>(b - a).count(); };
@@ -190,13 +216,16 @@ PB_API int pb_tonemap(pb_ctx* c, const float* frame, uint8_t* rgba8, uint32_t n,
 PB_API int pb_wait(pb_ctx* c) {
     if (!c) return PB_ERR_INVALID;
     cudaSetDevice(c->device);
-    return wavefront_wait(c);
+    int rc = wavefront_wait(c);
+    if (rc == PB_OK) rc = comm_poll(c);      // a peer that died or a failed link shows up here, not as a hang in the caller
+    return rc;
 }
 
 PB_API int pb_get_stats(pb_ctx* c, pb_stats* out) {
     if (!c || !out) return PB_ERR_INVALID;
     cudaSetDevice(c->device);
     int rc = wavefront_wait(c);
+    if (rc == PB_OK) rc = comm_poll(c);
     if (rc != PB_OK) return rc;
     *out = c->stats;
     return PB_OK;

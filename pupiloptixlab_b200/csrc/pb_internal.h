@@ -77,6 +77,12 @@ struct pb_ctx {
     uint32_t refill = 20;                // dynamic-fetch threshold (PB_REFILL overrides, tuning only)
     pb_stats stats{};
 
+    // ---- multi-GPU (pb_comm.cu): NCCL communicator of this context, film the reduce works on
+    void* nccl_comm = nullptr;           // ncclComm_t
+    int rank = 0, n_ranks = 1;
+    float* d_reduce = nullptr;           // w*h float4: this rank's frames of one PB_RENDER_REDUCE call, reduced in place
+    size_t reduce_px = 0;
+
     pb::TraceScene trace_scene() const {
         return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill, prim_batch, 0x47000000u, prim_iters};
     }
@@ -103,4 +109,12 @@ void wavefront_free(pb_ctx* c);
 int tonemap_frame(pb_ctx* c, const float* d_frame, uint8_t* d_rgba8, uint32_t n, int tone, int gamma, cudaStream_t s);
 int wavefront_wait(pb_ctx* c);   // synchronises pending (PB_RENDER_ASYNC) renders and folds them into pb_stats
 int resolve_frame(pb_ctx* c, const float* d_sum, float* d_frame, uint32_t n, cudaStream_t s);
+int film_add(pb_ctx* c, float* d_dst, const float* d_src, uint32_t n_px, cudaStream_t s);   // dst += src (float4 per pixel)
+// pb_comm.cu
+int comm_reserve_film(pb_ctx* c, size_t n_px);
+int comm_reduce_enqueue(pb_ctx* c, float* d_film, size_t n_px, cudaStream_t s);   // ncclReduce(sum, fp32, root 0), in place
+int comm_poll(pb_ctx* c);                                                          // asynchronous NCCL errors -> PB_ERR_NCCL
+void comm_free(pb_ctx* c);
+int comm_group_begin(pb_ctx* c);
+int comm_group_end(pb_ctx* c);
 }  // namespace pb

@@ -429,6 +429,16 @@ __global__ void __launch_bounds__(256) k_accumulate(WfState s, float4* sum, uint
     sum[pixel] = a;
 }
 
+// dst += src, float4 per pixel: the root's accumulation buffer takes the film NCCL reduced (pb_comm.cu)
+__global__ void k_film_add(float4* __restrict__ dst, const float4* __restrict__ src, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = dst[i];
+    const float4 b = src[i];
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    dst[i] = a;
+}
+
 __global__ void k_resolve(const float4* __restrict__ sum, float4* __restrict__ frame, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -667,6 +677,13 @@ __global__ void k_tonemap(const float4* __restrict__ frame, uchar4* __restrict__
 int tonemap_frame(pb_ctx* c, const float* d_frame, uint8_t* d_rgba8, uint32_t n, int tone, int gamma, cudaStream_t s) {
     if (n == 0) return PB_OK;
     k_tonemap<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float4*>(d_frame), reinterpret_cast<uchar4*>(d_rgba8), n, tone, gamma);
+    PB_CUDA_TRY(c, cudaGetLastError());
+    return PB_OK;
+}
+
+int film_add(pb_ctx* c, float* d_dst, const float* d_src, uint32_t n_px, cudaStream_t s) {
+    if (n_px == 0) return PB_OK;
+    k_film_add<<<(n_px + 255) / 256, 256, 0, s>>>(reinterpret_cast<float4*>(d_dst), reinterpret_cast<const float4*>(d_src), n_px);
     PB_CUDA_TRY(c, cudaGetLastError());
     return PB_OK;
 }

@@ -4,16 +4,42 @@
 namespace Pupil::pt {
 
 B200PTPass::B200PTPass(System* system, int device, std::string_view name) noexcept : Pass(name), m_system(system) {
-    // cuda::Context::Init + optix::Context::Init + PTPass ctor (pt_pass.cpp:29-37): one call
-    if (pb_create(&m_ctx, device) != PB_OK) { m_error = std::string("pb_create: ") + (m_ctx ? pb_last_error(m_ctx) : "no CUDA device (there is no CPU fallback)"); return; }
-    cudaSetDevice(device);
-    if (cudaStreamCreateWithFlags(&m_stream, cudaStreamNonBlocking) != cudaSuccess) m_error = "cudaStreamCreate failed";
+    init({device});
+}
+B200PTPass::B200PTPass(System* system, const std::vector<int>& devices, std::string_view name) noexcept : Pass(name), m_system(system) {
+    init(devices.empty() ? std::vector<int>{0} : devices);
+}
+
+// cuda::Context::Init + optix::Context::Init + PTPass ctor (pt_pass.cpp:29-37): one call per GPU
+void B200PTPass::init(const std::vector<int>& devices) noexcept {
+    m_devices = devices;
+    m_ctxs.assign(devices.size(), nullptr);
+    int rc;
+    if (devices.size() == 1) rc = pb_create(&m_ctxs[0], devices[0]);
+    else rc = pb_create_multi(m_ctxs.data(), devices.data(), static_cast<int>(devices.size()));
+    if (rc != PB_OK) {
+        m_error = rc == PB_ERR_NCCL ? "pb_create_multi: NCCL is not available or failed to initialise"
+                                    : std::string("pb_create: ") + (m_ctxs[0] ? pb_last_error(m_ctxs[0]) : "no CUDA device (there is no CPU fallback)");
+        for (auto& c : m_ctxs) { if (c) pb_destroy(c); c = nullptr; }
+        m_ctxs.clear();
+        return;
+    }
+    m_ctx = m_ctxs[0];
+    for (size_t i = 0; i < devices.size(); ++i) {
+        cudaSetDevice(devices[i]);
+        cudaStream_t st = nullptr;
+        if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) m_error = "cudaStreamCreate failed";
+        m_streams.push_back(st);
+    }
+    cudaSetDevice(devices[0]);
+    m_stream = m_streams.empty() ? nullptr : m_streams[0];
     BindingEventCallback();
 }
 
 B200PTPass::~B200PTPass() noexcept {
-    if (m_stream) cudaStreamDestroy(m_stream);
-    if (m_ctx) pb_destroy(m_ctx);
+    for (size_t i = 0; i < m_streams.size(); ++i) { cudaSetDevice(m_devices[i]); if (m_streams[i]) cudaStreamDestroy(m_streams[i]); }
+    for (pb_ctx* c : m_ctxs) if (c) pb_destroy(c);
+    if (!m_devices.empty()) cudaSetDevice(m_devices[0]);
 }
 
 void B200PTPass::fail(const char* what) noexcept {
@@ -46,7 +72,9 @@ void B200PTPass::SetScene(world::World* world) noexcept {
     const pupil::host::Scene& sc = *world->scene;
     std::string err;
     const ph_sink* sink = ph_default_sink();
-    if (pupil::host::upload_scene(sc, *sink, m_ctx, err) != PB_OK) { m_error = err + ": " + pb_last_error(m_ctx); m_system->last_error = m_error; return; }
+    for (pb_ctx* c : m_ctxs)      // replicated: every GPU ingests the same host data and builds the identical tree
+        if (pupil::host::upload_scene(sc, *sink, c, err) != PB_OK) { m_error = err + ": " + pb_last_error(c); m_system->last_error = m_error; return; }
+    cudaSetDevice(m_devices[0]);  // the BufferManager's buffers live on the first device
     m_w = static_cast<uint32_t>(sc.film_w); m_h = static_cast<uint32_t>(sc.film_h);
     max_depth = sc.max_depth;
     BufferManager& bm = m_system->buffers;
@@ -63,12 +91,15 @@ void B200PTPass::SetScene(world::World* world) noexcept {
 // pt_pass.cpp:39-57
 void B200PTPass::OnRun() noexcept {
     if (!m_ctx || !m_world || !m_error.empty()) return;
+    cudaSetDevice(m_devices[0]);
     if (m_dirty) {
-        for (auto& mv : m_moved)
-            if (pb_update_instance(m_ctx, mv.first, mv.second.e) != PB_OK) return fail("pb_update_instance");
-        m_moved.clear();
         const pupil::host::Mat4 s2c = m_world->camera.GetSampleToCameraMatrix(), c2w = m_world->camera.GetToWorldMatrix();
-        if (pb_set_camera(m_ctx, s2c.e, c2w.e) != PB_OK) return fail("pb_set_camera");
+        for (pb_ctx* c : m_ctxs) {
+            for (auto& mv : m_moved)
+                if (pb_update_instance(c, mv.first, mv.second.e) != PB_OK) { m_error = std::string("pb_update_instance: ") + pb_last_error(c); m_system->last_error = m_error; return; }
+            if (pb_set_camera(c, s2c.e, c2w.e) != PB_OK) { m_error = std::string("pb_set_camera: ") + pb_last_error(c); m_system->last_error = m_error; return; }
+        }
+        m_moved.clear();
         m_sample_cnt = 0;
         m_random_seed = 0;
         m_dirty = false;
@@ -82,7 +113,12 @@ void B200PTPass::OnRun() noexcept {
     p.flags = (m_sample_cnt == 0 || !accumulated_flag) ? PB_RENDER_CLEAR : 0u;
     const pb_render_targets tg{static_cast<float*>(m_accum->cuda_ptr), static_cast<float*>(m_albedo->cuda_ptr),
                                static_cast<float*>(m_normal->cuda_ptr), static_cast<float*>(m_test->cuda_ptr)};
-    if (pb_render_ex(m_ctx, &p, &tg, m_stream) != PB_OK) return fail("pb_render_ex");
+    if (m_ctxs.size() == 1) {
+        if (pb_render_ex(m_ctx, &p, &tg, m_stream) != PB_OK) return fail("pb_render_ex");
+    } else {   // the frames of this run dealt round-robin to the GPUs, one NCCL reduce into m_accum (rank 0)
+        std::vector<void*> streams(m_streams.begin(), m_streams.end());
+        if (pb_render_multi(m_ctxs.data(), static_cast<int>(m_ctxs.size()), &p, &tg, streams.data()) != PB_OK) return fail("pb_render_multi");
+    }
     if (pb_resolve(m_ctx, static_cast<const float*>(m_accum->cuda_ptr), static_cast<float*>(m_frame->cuda_ptr), m_w * m_h, 0, m_stream) != PB_OK)
         return fail("pb_resolve");
     if (accumulated_flag) m_sample_cnt += frames_per_run;   // sample_cnt += accumulated_flag (pt_pass.cpp:55)

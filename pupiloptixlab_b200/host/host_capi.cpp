@@ -119,13 +119,21 @@ struct ph_session {
 };
 
 PH_API int ph_session_create(const char* xml_path, int device, ph_session** out) {
+    return ph_session_create_multi(xml_path, &device, 1, out);
+}
+PH_API int ph_session_set_frames_per_run(ph_session* s, uint32_t frames) {
+    if (!s || !frames) return PB_ERR_INVALID;
+    s->pass->frames_per_run = frames;
+    return PB_OK;
+}
+PH_API int ph_session_create_multi(const char* xml_path, const int* devices, int n, ph_session** out) {
     using namespace Pupil;
     g_err.clear();
-    if (!xml_path || !out) return PB_ERR_INVALID;
+    if (!xml_path || !out || !devices || n < 1) return PB_ERR_INVALID;
     *out = nullptr;
     auto s = std::make_unique<ph_session>();
     s->system.Init(false);
-    s->pass = std::make_unique<pt::B200PTPass>(&s->system, device);
+    s->pass = std::make_unique<pt::B200PTPass>(&s->system, std::vector<int>(devices, devices + n));
     if (!s->pass->ok()) { g_err = s->pass->error(); return PB_ERR_NO_DEVICE; }
     s->system.AddPass(s->pass.get());
     if (!s->system.SetScene(xml_path) || !s->pass->ok()) {
