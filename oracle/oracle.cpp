@@ -911,9 +911,18 @@ ORC_API int orc_import_cwbvh(orc_ctx* c, const void* nodes80, uint64_t n_nodes, 
         if (gid >= n_prims || seen[gid]) { b = CwBvh{}; c->err = "exported leaf records do not hold every primitive id exactly once"; return PB_ERR_INVALID; }
         seen[gid] = 1;
         const Prim& p = c->prims[gid];
-        const float want[9] = {p.v0.x, p.v0.y, p.v0.z, p.v1.x, p.v1.y, p.v1.z, p.v2.x, p.v2.y, p.v2.z};
+        float want[9] = {p.v0.x, p.v0.y, p.v0.z, p.v1.x, p.v1.y, p.v1.z, p.v2.x, p.v2.y, p.v2.z};
         const float got[9] = {r[0], r[1], r[2], r[4], r[5], r[6], r[8], r[9], r[10]};
-        if (kind != p.kind || obj != p.obj || memcmp(want, got, 36) != 0) {
+        uint32_t want_kind = p.kind;
+        if (kind == 2u && p.kind == 1u && obj < c->objects.size()) {
+            // "uniform sphere" record of the product: centre | (extent, 1/s, 0) | translation of world->object.  Legal only
+            // where this scene's own world->object matrix is (1/s) * identity + translation; then it must carry those values.
+            const float* I = c->objects[obj].Minv;
+            const bool uniform = I[1] == 0.f && I[2] == 0.f && I[4] == 0.f && I[6] == 0.f && I[8] == 0.f && I[9] == 0.f && I[0] == I[5] && I[0] == I[10] &&
+                                 p.v1.x == p.v1.y && p.v1.x == p.v1.z;
+            if (uniform) { want_kind = 2u; want[4] = I[0]; want[5] = 0.f; want[6] = I[3]; want[7] = I[7]; want[8] = I[11]; }
+        }
+        if (kind != want_kind || obj != p.obj || memcmp(want, got, 36) != 0) {
             b = CwBvh{}; c->err = "exported primitive record " + std::to_string(i) + " differs from the oracle's world-space primitive " + std::to_string(gid);
             return PB_ERR_INVALID;
         }

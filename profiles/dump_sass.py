@@ -20,16 +20,36 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "pupiloptixlab_b200", "csrc")
 OUT = os.path.join(ROOT, "profiles", "sass")
 
+# (object, regex on the DEMANGLED kernel name, listing name): symbols are looked up in the object, so a changed parameter
+# list cannot silently produce an empty listing (round 1's k_accumulate.sass)
 KERNELS = [
-    ("pb_wavefront.o", "_ZN2pb8k_extendILb0EEEvNS_7WfStateENS_7WfSceneEi", "k_extend"),
-    ("pb_wavefront.o", "_ZN2pb9k_connectILb0EEEvNS_7WfStateENS_7WfSceneE", "k_connect"),
-    ("pb_trace.o", "_ZN2pb7k_traceILb0ELb0EEEvNS_10TraceSceneEPK6float4jPS2_PhPy", "k_trace_closest"),
-    ("pb_trace.o", "_ZN2pb7k_traceILb1ELb0EEEvNS_10TraceSceneEPK6float4jPS2_PhPy", "k_trace_any"),
-    ("pb_wavefront.o", "_ZN2pb7k_shadeILi1EEEvNS_7WfStateENS_7WfSceneEijPfS3_", "k_shade_1_diffuse"),
-    ("pb_wavefront.o", "_ZN2pb7k_shadeILi3EEEvNS_7WfStateENS_7WfSceneEijPfS3_", "k_shade_3_rough_dielectric"),
-    ("pb_wavefront.o", "_ZN2pb10k_generateENS_7WfStateENS_7WfSceneEj", "k_generate"),
-    ("pb_wavefront.o", "_ZN2pb12k_accumulateENS_7WfStateEP6float4jj", "k_accumulate"),
+    ("pb_wavefront.o", r"pb::k_extend<false>", "k_extend"),
+    ("pb_wavefront.o", r"pb::k_connect<false>", "k_connect"),
+    ("pb_trace.o", r"pb::k_trace<false, false>", "k_trace_closest"),
+    ("pb_trace.o", r"pb::k_trace<true, false>", "k_trace_any"),
+    ("pb_wavefront.o", r"pb::k_shade<1>", "k_shade_1_diffuse"),
+    ("pb_wavefront.o", r"pb::k_shade<3>", "k_shade_3_rough_dielectric"),
+    ("pb_wavefront.o", r"pb::k_shade<7>", "k_shade_7_rough_plastic"),
+    ("pb_wavefront.o", r"pb::k_generate\(", "k_generate"),
+    ("pb_wavefront.o", r"pb::k_accumulate\(", "k_accumulate"),
+    ("pb_wavefront.o", r"pb::k_write_aov\(", "k_write_aov"),
+    ("pb_wavefront.o", r"pb::k_miss\(", "k_miss"),
+    ("pb_build.o", r"pb::k_refit_wide", "k_refit_wide"),
+    ("pb_build.o", r"pb::k_update_prims", "k_update_prims"),
 ]
+OPTIONAL = {"k_refit_wide", "k_update_prims"}
+
+
+def find_symbol(obj_path: str, rx: str) -> str | None:
+    """Mangled name of the kernel whose demangled name matches rx."""
+    out = subprocess.run(["cuobjdump", "-elf", obj_path], capture_output=True, text=True).stdout
+    names = sorted(set(re.findall(r"\.text\.(_Z\w+)", out)))
+    dem = subprocess.run(["c++filt"], input="\n".join(names), capture_output=True, text=True).stdout.splitlines()
+    for m, d in zip(names, dem):
+        if re.search(rx, d):
+            return m
+    return None
+
 
 CALL_OUT = [
     ("LDG.E.128 / LDG.E.ENL2.256 (vector global loads)", r"^LDG\.E\.(128|ENL2\.256)"),
@@ -59,10 +79,15 @@ def main():
     lines_md = ["# SASS listings of the hot kernels (sm_100a, nvcc 12.9, `-O3 -fmad=false -lineinfo`)", "",
                 "Written by `profiles/dump_sass.py` from the objects `pupiloptixlab_b200/build.py` produces; one",
                 "`<kernel>.sass` per kernel next to this file.  Counts are static instructions in the listing.", ""]
-    for obj, mangled, name in KERNELS:
+    for obj, rx, name in KERNELS:
         path = os.path.join(CSRC, obj)
         if not os.path.exists(path):
             sys.exit(f"{path} missing: run python -m pupiloptixlab_b200.build first")
+        mangled = find_symbol(path, rx)
+        if mangled is None:
+            if name in OPTIONAL:
+                continue
+            sys.exit(f"no kernel matching {rx!r} in {obj}")
         raw = sh("cuobjdump", "-sass", "-fun", mangled, path)
         res = sh("cuobjdump", "-res-usage", "-fun", mangled, path)
         usage = " ".join(l.strip() for l in res.splitlines() if "REG:" in l)
@@ -79,6 +104,8 @@ def main():
                 continue                                         # second half of the 128-bit encoding
             elif l.strip().startswith((".L_", "Function", ".headerflags")):
                 listing.append(l.strip())
+        if not listing:
+            sys.exit(f"empty listing for {name} ({mangled})")
         with open(os.path.join(OUT, name + ".sass"), "w") as f:
             f.write(f"// {name}  ({mangled})\n// {usage}\n" + "\n".join(listing) + "\n")
         total = sum(ops.values())

@@ -80,9 +80,32 @@ PB_HD bool sphere_test(V3 ro, V3 rd, float tmin, float tmax, const float* Minv, 
     return false;
 }
 
+// the same test when world->object is inv * identity + (tx, ty, tz): sphere_test with the terms that multiply the
+// zero entries of Minv left out.  fma(0, y, fma(0, z, t)) == t and fma(0, y, 0 * z) == +-0 exactly, so o and d — and with
+// them a, b, c, the discriminant and both roots — are the values sphere_test computes, bit for bit (a zero's sign cannot
+// reach t: it only enters sums with non-zero terms or squares).
+PB_HD bool sphere_test_uniform(V3 ro, V3 rd, float tmin, float tmax, float inv, V3 tr, float& t) {
+    V3 o = {f_fma(inv, ro.x, tr.x), f_fma(inv, ro.y, tr.y), f_fma(inv, ro.z, tr.z)};
+    V3 d = {f_mul(inv, rd.x), f_mul(inv, rd.y), f_mul(inv, rd.z)};
+    float a = dot_fma(d, d);
+    float b = dot_fma(o, d);
+    float c = f_sub(dot_fma(o, o), 1.0f);
+    float disc = f_fma(b, b, -f_mul(a, c));
+    if (!(disc >= 0.f) || a == 0.f) return false;
+    float s = f_sqrt(disc);
+    float t0 = f_div(f_sub(-b, s), a);
+    if (t0 > tmin && t0 < tmax) { t = t0; return true; }
+    float t1 = f_div(f_add(-b, s), a);
+    if (t1 > tmin && t1 < tmax) { t = t1; return true; }
+    return false;
+}
+
 // exact bbox of a primitive record (before padding)
 PB_HD void prim_bbox(const PrimRec& r, V3& lo, V3& hi) {
-    if (f2u(r.c.w) == PRIM_TRI) {
+    if (f2u(r.c.w) == PRIM_SPHERE_UNIFORM) {
+        lo = {f_sub(r.a.x, r.b.x), f_sub(r.a.y, r.b.x), f_sub(r.a.z, r.b.x)};
+        hi = {f_add(r.a.x, r.b.x), f_add(r.a.y, r.b.x), f_add(r.a.z, r.b.x)};
+    } else if (f2u(r.c.w) == PRIM_TRI) {
         lo = {fminf(fminf(r.a.x, r.b.x), r.c.x), fminf(fminf(r.a.y, r.b.y), r.c.y), fminf(fminf(r.a.z, r.b.z), r.c.z)};
         hi = {fmaxf(fmaxf(r.a.x, r.b.x), r.c.x), fmaxf(fmaxf(r.a.y, r.b.y), r.c.y), fmaxf(fmaxf(r.a.z, r.b.z), r.c.z)};
     } else {
@@ -110,6 +133,9 @@ PB_HD bool prim_accept(const PrimRec& r, const ObjRec* objs, V3 o, V3 d, const R
     if (!(N <= F) || !(F > tmin) || !(N < tmax) || N > t_best) return false;
     if (f2u(r.c.w) == PRIM_TRI) {
         if (!tri_test(o, d, tmin, tmax, {r.a.x, r.a.y, r.a.z}, {r.b.x, r.b.y, r.b.z}, {r.c.x, r.c.y, r.c.z}, t, u, v)) return false;
+    } else if (f2u(r.c.w) == PRIM_SPHERE_UNIFORM) {
+        u = 0.f; v = 0.f;
+        if (!sphere_test_uniform(o, d, tmin, tmax, r.b.y, {r.c.x, r.c.y, r.c.z}, t)) return false;
     } else {
         u = 0.f; v = 0.f;
 #if defined(__CUDA_ARCH__)

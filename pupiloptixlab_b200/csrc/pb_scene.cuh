@@ -43,6 +43,17 @@ PB_HD PrimRec make_prim(const SceneGeom& g, uint32_t prim) {
         r.a = {o.M[3], o.M[7], o.M[11], u2f(prim)};
         r.b = {f_sqrt(dot_fma(r0, r0)), f_sqrt(dot_fma(r1, r1)), f_sqrt(dot_fma(r2, r2)), u2f(oi)};
         r.c = {0.f, 0.f, 0.f, u2f(PRIM_SPHERE)};
+        // linear part s * identity: world->object is (1/s) * identity + translation, its off-diagonal terms are +-0 and
+        // drop out of the general test without changing a bit (pb_intersect.cuh)
+        const float* I = o.Minv;
+        const bool uniform = o.M[1] == 0.f && o.M[2] == 0.f && o.M[4] == 0.f && o.M[6] == 0.f && o.M[8] == 0.f && o.M[9] == 0.f &&
+                             o.M[0] == o.M[5] && o.M[0] == o.M[10] && o.M[0] != 0.f &&
+                             I[1] == 0.f && I[2] == 0.f && I[4] == 0.f && I[6] == 0.f && I[8] == 0.f && I[9] == 0.f &&
+                             I[0] == I[5] && I[0] == I[10] && r.b.x == r.b.y && r.b.x == r.b.z;
+        if (uniform) {
+            r.b = {r.b.x, I[0], 0.f, u2f(oi)};
+            r.c = {I[3], I[7], I[11], u2f(PRIM_SPHERE_UNIFORM)};
+        }
     } else {
         const uint32_t* t = g.idx + 3ull * (o.index_offset + (prim - o.prim_offset));
         const float* p = g.pos + 3ull * o.vert_offset;

@@ -103,9 +103,15 @@ static_assert(sizeof(Node8) == 80, "Node8 must be 80 bytes");
 // ---- primitive in leaf order, 48 bytes ----------------------------------------------------------
 // triangle: a = (v0, prim id), b = (v1, object id), c = (v2, kind = 0)
 // sphere  : a = (centre, prim id), b = (half extents of the world box, object id), c = (0,0,0, kind = 1)
+// sphere whose object->world linear part is s * identity (what ShapeLoader<_sphere> produces, shape.cpp:106-125, unless
+//           the XML adds a rotation / non-uniform scale): a = (centre, prim id), b = (|s| = every half extent, 1/s = the
+//           diagonal of world->object, 0, object id), c = (translation column of world->object, kind = 2).  The record
+//           then holds everything the unit-sphere test needs (pb_intersect.cuh sphere_test_uniform): no dependent fetch
+//           of the object's inverse matrix, and the arithmetic is the general path's with its zero terms dropped,
+//           i.e. bit-identical results (the oracle keeps the general form only).
 struct alignas(16) PrimRec { V4 a, b, c; };
 static_assert(sizeof(PrimRec) == 48, "PrimRec must be 48 bytes");
-enum { PRIM_TRI = 0u, PRIM_SPHERE = 1u };
+enum { PRIM_TRI = 0u, PRIM_SPHERE = 1u, PRIM_SPHERE_UNIFORM = 2u };
 
 // ---- textures / materials / objects / emitters --------------------------------------------------
 struct TexRec {          // 64 B; mirror of cuda::Texture (framework/cuda/texture.h:9-31)

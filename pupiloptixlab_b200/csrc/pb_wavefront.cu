@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfS
 
 // ---- shade<MAT>: one path vertex.  Follows main.cu:84-183 line by line -----------------------------------
 template<int MAT>
-__global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfState s, WfScene sc, int cur, uint32_t k_aov, AovOut aov) {
+__global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfState s, WfScene sc, int cur) {
     const uint32_t n = s.cnt[C_MAT0 + MAT];
     const uint32_t* q = s.q_mat + (size_t)MAT * s.cap;
     uint32_t* qnext = cur ? s.q_ext[0] : s.q_ext[1];
@@ -298,15 +298,8 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
             int depth = (int)(fl & F_DEPTH_MASK);
             if (depth == 0) {  // primary hit: main.cu:87-101
                 if (emitter_index >= 0) radiance += emitter_radiance(sc.em.rec[emitter_index], geo.texcoord);
-                uint32_t k, j;
-                slot_to_kj(slot, sc.n_px, sc.kw, k, j);
-                const float test_value = rng.next();  // test[pixel] = rng.Next(), main.cu:101
-                if (k == k_aov) {
-                    const uint32_t pixel = path_pixel(j, sc.width, sc.height);
-                    if (aov.albedo) { const V3 a = bsdf_albedo<MAT>(bsdf); aov.albedo[3 * pixel] = a.x; aov.albedo[3 * pixel + 1] = a.y; aov.albedo[3 * pixel + 2] = a.z; }
-                    if (aov.normal) { aov.normal[3 * pixel] = geo.normal.x; aov.normal[3 * pixel + 1] = geo.normal.y; aov.normal[3 * pixel + 2] = geo.normal.z; }
-                    if (aov.test) aov.test[pixel] = test_value;
-                }
+                (void)rng.next();  // test[pixel] = rng.Next(), main.cu:101 — the AOVs themselves (main.cu:94-101) are written by
+                                   // k_write_aov for the one frame that needs them: no slot -> pixel arithmetic in the shade kernels
             } else if (emitter_index >= 0) {  // emitter hit by the BSDF sample: main.cu:171-182
                 const EmitRec& e = sc.em.rec[emitter_index];
                 EmitEval ev;
@@ -379,8 +372,43 @@ __global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfSta
     }
 }
 
+// ---- aov: albedo / normal / test of the primary hits of ONE frame of the wave (main.cu:94-101), between the first extend and
+// the first shade (which overwrites the camera ray).  n_px threads, once per pb_render call: the seven shade kernels carry
+// no pixel arithmetic for it.
+template<int MAT>
+__device__ __forceinline__ V3 aov_albedo(const MatRec& m, V2 uv) { return bsdf_albedo<MAT>(bsdf_local<MAT>(m, uv)); }
+
+__global__ void __launch_bounds__(256) k_write_aov(WfState s, WfScene sc, uint32_t k_aov_frame, AovOut aov) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= sc.n_px) return;
+    const uint32_t pixel = path_pixel(j, sc.width, sc.height);
+    const float4* rec = s.rec + (size_t)R_COUNT * kj_to_slot(k_aov_frame, j, sc.n_px, sc.kw);
+    const float4 ro4 = rec[R_ORG], rd4 = rec[R_DIR], h4 = rec[R_HIT], ob4 = rec[R_OBJ];
+    V3 albedo = v3(0.f), normal = v3(0.f);
+    const uint32_t prim = __float_as_uint(h4.w);
+    if (prim != 0xFFFFFFFFu) {
+        const ObjRec& o = sc.geom.objs[__float_as_uint(ob4.x)];
+        const MatRec& m = sc.mats[o.material];
+        const LocalGeo geo = hit_geometry(sc.geom, o, prim, h4.x, h4.y, h4.z, v3(ro4.x, ro4.y, ro4.z), v3(rd4.x, rd4.y, rd4.z), m.twosided != 0u);
+        normal = geo.normal;
+        switch (m.type) {   // Material::GetLocalBsdf + LocalBsdf::GetAlbedo, optix_material.h:69-106
+            case MAT_DIFFUSE: albedo = aov_albedo<MAT_DIFFUSE>(m, geo.texcoord); break;
+            case MAT_DIELECTRIC: albedo = aov_albedo<MAT_DIELECTRIC>(m, geo.texcoord); break;
+            case MAT_ROUGH_DIELECTRIC: albedo = aov_albedo<MAT_ROUGH_DIELECTRIC>(m, geo.texcoord); break;
+            case MAT_CONDUCTOR: albedo = aov_albedo<MAT_CONDUCTOR>(m, geo.texcoord); break;
+            case MAT_ROUGH_CONDUCTOR: albedo = aov_albedo<MAT_ROUGH_CONDUCTOR>(m, geo.texcoord); break;
+            case MAT_PLASTIC: albedo = aov_albedo<MAT_PLASTIC>(m, geo.texcoord); break;
+            case MAT_ROUGH_PLASTIC: albedo = aov_albedo<MAT_ROUGH_PLASTIC>(m, geo.texcoord); break;
+            default: break;
+        }
+    }
+    if (aov.albedo) { aov.albedo[3 * pixel] = albedo.x; aov.albedo[3 * pixel + 1] = albedo.y; aov.albedo[3 * pixel + 2] = albedo.z; }
+    if (aov.normal) { aov.normal[3 * pixel] = normal.x; aov.normal[3 * pixel + 1] = normal.y; aov.normal[3 * pixel + 2] = normal.z; }
+    if (aov.test) { Rng rng; rng.s = __float_as_uint(rec[R_RAD].w); aov.test[pixel] = rng.next(); }   // the draw behind the two jitter draws, hit or miss
+}
+
 // ---- miss: __miss__default (main.cu:196-212) + main.cu:165-169,185 ----------------------------------------
-__global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_aov, AovOut aov) {
+__global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc) {
     const uint32_t n = s.cnt[C_MAT0];
     const EmitRec& env = sc.em.rec[sc.em.n_area];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -390,16 +418,6 @@ __global__ void __launch_bounds__(256) k_miss(WfState s, WfScene sc, uint32_t k_
         ld256(rec + R_ORG, ro4, rd4);
         const uint32_t fl = __float_as_uint(ro4.w);
         const bool primary = (fl & F_DEPTH_MASK) == 0u;
-        if (primary) {
-            uint32_t k, j;
-            slot_to_kj(slot, sc.n_px, sc.kw, k, j);
-            if (k == k_aov) {
-                const uint32_t pixel = path_pixel(j, sc.width, sc.height);
-                if (aov.albedo) { aov.albedo[3 * pixel] = 0.f; aov.albedo[3 * pixel + 1] = 0.f; aov.albedo[3 * pixel + 2] = 0.f; }
-                if (aov.normal) { aov.normal[3 * pixel] = 0.f; aov.normal[3 * pixel + 1] = 0.f; aov.normal[3 * pixel + 2] = 0.f; }
-                if (aov.test) { Rng rng; rng.s = __float_as_uint(rec[R_RAD].w); aov.test[pixel] = rng.next(); }   // main.cu:101 runs for misses too
-            }
-        }
         if (env.type == EM_NONE) continue;
         const V3 ray_o = {ro4.x, ro4.y, ro4.z}, rd = normalize(v3(rd4.x, rd4.y, rd4.z));
         EmitEval ev;
@@ -529,8 +547,8 @@ static int wavefront_reserve(pb_ctx* c, uint32_t cap) {
 }
 
 template<int MAT>
-static void launch_shade(const WfState& st, const WfScene& sc, int cur, uint32_t k_aov, const AovOut& aov, unsigned grid, cudaStream_t s) {
-    k_shade<MAT><<<grid, kWfThreads, 0, s>>>(st, sc, cur, k_aov, aov);
+static void launch_shade(const WfState& st, const WfScene& sc, int cur, unsigned grid, cudaStream_t s) {
+    k_shade<MAT><<<grid, kWfThreads, 0, s>>>(st, sc, cur);
 }
 
 int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* d_albedo, float* d_normal, float* d_test, cudaStream_t s) {
@@ -599,6 +617,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
         const uint32_t k_aov = last_wave ? kw - 1 : 0xFFFFFFFFu;   // AOVs of the last frame (main.cu:94-99)
         k_set_frame0<<<1, 1, 0, s>>>(st, p->first_sample + k0 * sc.stride);
         ++launches;
+        const bool want_aov = k_aov != 0xFFFFFFFFu && (aov.albedo || aov.normal || aov.test);
         auto enqueue_wave = [&]() {
             k_generate<<<(n_paths + 255) / 256, 256, 0, s>>>(st, sc, n_paths);
             int cur = 0;
@@ -608,15 +627,16 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
                 if (counted) k_extend<true><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
                 else k_extend<false><<<g_trace, kWfThreads, 0, s>>>(st, sc, cur);
                 mark(ev_ext);
+                if (b == 0 && want_aov) k_write_aov<<<(n_px + 255) / 256, 256, 0, s>>>(st, sc, k_aov, aov);
                 mark(ev_shd);
-                k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc, k_aov, aov);
-                launch_shade<1>(st, sc, cur, k_aov, aov, g_shade, s);
-                launch_shade<2>(st, sc, cur, k_aov, aov, g_shade, s);
-                launch_shade<3>(st, sc, cur, k_aov, aov, g_shade, s);
-                launch_shade<4>(st, sc, cur, k_aov, aov, g_shade, s);
-                launch_shade<5>(st, sc, cur, k_aov, aov, g_shade, s);
-                launch_shade<6>(st, sc, cur, k_aov, aov, g_shade, s);
-                launch_shade<7>(st, sc, cur, k_aov, aov, g_shade, s);
+                k_miss<<<(unsigned)c->sm_count * 4u, 256, 0, s>>>(st, sc);
+                launch_shade<1>(st, sc, cur, g_shade, s);
+                launch_shade<2>(st, sc, cur, g_shade, s);
+                launch_shade<3>(st, sc, cur, g_shade, s);
+                launch_shade<4>(st, sc, cur, g_shade, s);
+                launch_shade<5>(st, sc, cur, g_shade, s);
+                launch_shade<6>(st, sc, cur, g_shade, s);
+                launch_shade<7>(st, sc, cur, g_shade, s);
                 k_after_shade<<<1, 1, 0, s>>>(st);
                 mark(ev_shd);
                 mark(ev_con);
@@ -627,7 +647,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
             }
             k_accumulate<<<(n_px + 255) / 256, 256, 0, s>>>(st, reinterpret_cast<float4*>(d_sum), p->width, p->height, kw);
         };
-        launches += 2u + 12u * n_bounces;
+        launches += 2u + 12u * n_bounces + (want_aov ? 1u : 0u);
         cudaGraphExec_t exec = nullptr;
         if (use_graph) {
             for (auto& g : c->wf->graphs)
