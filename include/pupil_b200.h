@@ -152,6 +152,9 @@ typedef struct pb_stats {
     uint32_t extend_launches, connect_launches;
     float    shade_ms;                      /* miss + the seven shade launches of every bounce   */
     uint32_t shade_groups;
+    /* how pb_update_instance was served since the last pb_scene_commit: refits in place (IAS::Update semantics) and
+     * full rebuilds (the move changed the scene box enough to change the contract's padding delta)               */
+    uint32_t refits, rebuilds;
 } pb_stats;
 
 typedef struct pb_ctx pb_ctx;
@@ -184,7 +187,12 @@ PB_API int pb_set_camera(pb_ctx* ctx, const float sample_to_camera[16], const fl
 /* emitter tables (EmitterHelper::ComputeProbability, world/emitter.cpp:321-337) + device BVH
  * build (replaces optixAccelBuild, world/gas_manager.cpp:151, world/ias_manager.cpp:84)          */
 PB_API int pb_scene_commit(pb_ctx* ctx);
-/* IAS::Update analogue (world/ias_manager.cpp:116-151): new transform, then rebuild on device    */
+/* IAS::Update analogue (world/ias_manager.cpp:116-151,187-205; RenderObject::UpdateTransform, world/render_object.cpp:46-49):
+ * new object->world transform of one object.  Served by a REFIT: the object's world-space leaf records are rewritten in
+ * place and every node's child boxes are recomputed bottom-up (no sort, no collapse, no allocation; device pointers
+ * and captured wave graphs stay valid; < 1 ms at 10 M primitives); area-emitter tables of a moved light are rewritten
+ * in place.  Falls back to a full rebuild only when the move changes the scene's largest extent, i.e. delta, the
+ * padding of the intersection contract (pb_stats.refits / .rebuilds tell which).  Results never depend on the tree.  */
 PB_API int pb_update_instance(pb_ctx* ctx, uint32_t object, const float to_world[12]);
 
 /* ---- ray casting.  Replaces optixTrace ray type 0 (path_tracer/main.cu:77,158) and ray type 1

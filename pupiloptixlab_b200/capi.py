@@ -64,7 +64,7 @@ class Stats(C.Structure):
                 ("node_visits_any", C.c_uint64), ("prim_tests_tri_any", C.c_uint64), ("prim_tests_sphere_any", C.c_uint64),
                 ("extend_ms", C.c_float), ("connect_ms", C.c_float),
                 ("extend_launches", C.c_uint32), ("connect_launches", C.c_uint32),
-                ("shade_ms", C.c_float), ("shade_groups", C.c_uint32)]
+                ("shade_ms", C.c_float), ("shade_groups", C.c_uint32), ("refits", C.c_uint32), ("rebuilds", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -36,6 +36,7 @@ PB_API int pb_create(pb_ctx** out, int device) {
     if (const char* e = getenv("PB_LEAF_MAX")) { int v = atoi(e); if (v >= 1 && v <= 3) c->leaf_max = (uint32_t)v; }
     if (const char* e = getenv("PB_BOTTOM_MAX")) { int v = atoi(e); if (v >= 0 && v <= 24) c->bottom_max = (uint32_t)v; }
     if (getenv("PB_NO_GRAPH")) c->use_graphs = false;
+    if (getenv("PB_NO_REFIT")) c->allow_refit = false;
     if (const char* e = getenv("PB_REFILL")) { int v = atoi(e); if (v >= 1 && v <= 32) c->refill = (uint32_t)v; }
     return PB_OK;
 }
@@ -45,6 +46,9 @@ static void free_device_scene(pb_ctx* c) {
     cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_idx);
     cudaFree(c->d_objs); cudaFree(c->d_mats); cudaFree(c->d_emit); cudaFree(c->d_emit_prefix); cudaFree(c->d_env_tables);
     cudaFree(c->d_nodes); cudaFree(c->d_prims);
+    cudaFree(c->d_node_lo); cudaFree(c->d_node_hi); cudaFree(c->d_obj_box);
+    c->d_node_lo = c->d_node_hi = nullptr; c->d_obj_box = nullptr;
+    c->level_first.clear(); c->h_obj_lo.clear(); c->h_obj_hi.clear();
     c->d_pos = c->d_nrm = c->d_uv = nullptr; c->d_idx = nullptr; c->d_objs = nullptr; c->d_mats = nullptr;
     c->d_emit = nullptr; c->d_emit_prefix = nullptr; c->d_env_tables = nullptr; c->d_nodes = nullptr; c->d_prims = nullptr;
     for (float* b : c->d_bitmaps) cudaFree(b);

@@ -107,6 +107,28 @@ PB_HD uint32_t quant_exponent(float ext) {
     return (uint32_t)e;
 }
 
+// Quantisation frame of a wide node whose children span [lo, hi]: origin = lo, one power-of-two scale per axis such that
+// every child maximum fits in 8 bits (checked exactly in double).  Used by the build and by the refit.
+PB_HD void node_frame(Node8& nd, V3 lo, V3 hi) {
+    nd.px = lo.x; nd.py = lo.y; nd.pz = lo.z;
+    uint32_t ex = quant_exponent(hi.x - lo.x), ey = quant_exponent(hi.y - lo.y), ez = quant_exponent(hi.z - lo.z);
+    for (int axis = 0; axis < 3; ++axis) {
+        uint32_t& e = axis == 0 ? ex : (axis == 1 ? ey : ez);
+        const double p = axis == 0 ? lo.x : (axis == 1 ? lo.y : lo.z);
+        const double h = axis == 0 ? hi.x : (axis == 1 ? hi.y : hi.z);
+        while (e < 254u && ceil((h - p) / (double)u2f(e << 23)) > 255.0) ++e;
+    }
+    nd.ex = (uint8_t)ex; nd.ey = (uint8_t)ey; nd.ez = (uint8_t)ez;
+}
+// child box of slot s in the node's frame, rounded outward
+PB_HD void node_quantise_slot(Node8& nd, int s, V3 clo, V3 chi) {
+    const double sx = u2f((uint32_t)nd.ex << 23), sy = u2f((uint32_t)nd.ey << 23), sz = u2f((uint32_t)nd.ez << 23);
+    auto qlo = [](float v, double p, double sc) { double q = floor(((double)v - p) / sc); return (uint8_t)(q < 0.0 ? 0.0 : (q > 255.0 ? 255.0 : q)); };
+    auto qhi = [](float v, double p, double sc) { double q = ceil(((double)v - p) / sc); return (uint8_t)(q < 0.0 ? 0.0 : (q > 255.0 ? 255.0 : q)); };
+    nd.qlox[s] = qlo(clo.x, nd.px, sx); nd.qloy[s] = qlo(clo.y, nd.py, sy); nd.qloz[s] = qlo(clo.z, nd.pz, sz);
+    nd.qhix[s] = qhi(chi.x, nd.px, sx); nd.qhiy[s] = qhi(chi.y, nd.py, sy); nd.qhiz[s] = qhi(chi.z, nd.pz, sz);
+}
+
 PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t w, uint32_t off_inner, uint32_t off_prims) {
     uint32_t ch[8];
     V3 clo[8], chi[8];
@@ -144,17 +166,7 @@ PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t
     }
     // ---- quantisation grid
     Node8 nd;
-    nd.px = lo.x; nd.py = lo.y; nd.pz = lo.z;
-    uint32_t ex = quant_exponent(hi.x - lo.x), ey = quant_exponent(hi.y - lo.y), ez = quant_exponent(hi.z - lo.z);
-    // exact (double) check that every child maximum fits in 8 bits; bump the exponent otherwise
-    for (int axis = 0; axis < 3; ++axis) {
-        uint32_t& e = axis == 0 ? ex : (axis == 1 ? ey : ez);
-        const double p = axis == 0 ? lo.x : (axis == 1 ? lo.y : lo.z);
-        const double h = axis == 0 ? hi.x : (axis == 1 ? hi.y : hi.z);
-        while (e < 254u && ceil((h - p) / (double)u2f(e << 23)) > 255.0) ++e;
-    }
-    nd.ex = (uint8_t)ex; nd.ey = (uint8_t)ey; nd.ez = (uint8_t)ez;
-    const double sx = u2f(ex << 23), sy = u2f(ey << 23), sz = u2f(ez << 23);
+    node_frame(nd, lo, hi);
     uint32_t imask = 0, pmask = 0;
     for (int s = 0; s < 8; ++s) {
         nd.qlox[s] = nd.qloy[s] = nd.qloz[s] = 0;
@@ -166,10 +178,7 @@ PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t
         int k = -1;
         for (int q = 0; q < n; ++q) if (slot_of[q] == s) k = q;
         if (k < 0) continue;
-        auto qlo = [](float v, double p, double sc) { double q = floor(((double)v - p) / sc); return (uint8_t)(q < 0.0 ? 0.0 : (q > 255.0 ? 255.0 : q)); };
-        auto qhi = [](float v, double p, double sc) { double q = ceil(((double)v - p) / sc); return (uint8_t)(q < 0.0 ? 0.0 : (q > 255.0 ? 255.0 : q)); };
-        nd.qlox[s] = qlo(clo[k].x, lo.x, sx); nd.qloy[s] = qlo(clo[k].y, lo.y, sy); nd.qloz[s] = qlo(clo[k].z, lo.z, sz);
-        nd.qhix[s] = qhi(chi[k].x, lo.x, sx); nd.qhiy[s] = qhi(chi[k].y, lo.y, sy); nd.qhiz[s] = qhi(chi[k].z, lo.z, sz);
+        node_quantise_slot(nd, s, clo[k], chi[k]);
         if (!(ch[k] & kLeafFlag)) {
             imask |= 1u << s;
             c.next_work[off_inner + inner_rank] = {ch[k], c.next_wide_base + off_inner + inner_rank};
@@ -187,6 +196,52 @@ PB_HD void collapse_emit(const BuildArrays& b, const CollapseArrays& c, uint32_t
     nd.child_base = c.next_wide_base + off_inner;
     nd.prim_base = c.prim_cursor + off_prims;
     c.nodes[c.work[w].wide_index] = nd;
+}
+
+// ---- refit: IAS::Update semantics (framework/world/ias_manager.cpp:116-151: optixAccelBuild in UPDATE mode keeps the
+// topology and recomputes the bounds) for the flattened 8-wide tree.  One node: child boxes from the leaf slots' (already
+// rewritten) primitives and from the inner children's boxes of the level below, new quantisation frame, same slots /
+// masks / bases.  `box` holds one (lo, hi) pair per node; levels are processed bottom-up.
+PB_HD void refit_wide_node(Node8* nodes, const PrimRec* prims, V3* box_lo, V3* box_hi, float delta, uint32_t i) {
+    Node8 nd = nodes[i];
+    V3 clo[8], chi[8];
+    bool used[8];
+    const float fm = 3.402823466e38f;
+    V3 lo = v3(fm), hi = v3(-fm);
+    uint32_t rank = 0, prim_off = 0;
+    for (int s = 0; s < 8; ++s) {
+        used[s] = false;
+        const uint32_t cnt = (uint32_t)pop_cnt((nd.pmask >> (3 * s)) & 7u);
+        if ((nd.imask >> s) & 1u) {
+            const uint32_t ch = nd.child_base + rank++;
+            clo[s] = box_lo[ch]; chi[s] = box_hi[ch];
+            used[s] = true;
+        } else if (cnt) {
+            V3 l = v3(fm), h = v3(-fm);
+            for (uint32_t j = 0; j < cnt; ++j) {
+                V3 pl, ph;
+                prim_bbox(prims[nd.prim_base + prim_off + j], pl, ph);
+                pad_box(pl, ph, 2.0f * delta);            // B_out, as build_prim pads it
+                l = {fminf(l.x, pl.x), fminf(l.y, pl.y), fminf(l.z, pl.z)};
+                h = {fmaxf(h.x, ph.x), fmaxf(h.y, ph.y), fmaxf(h.z, ph.z)};
+            }
+            prim_off += cnt;
+            clo[s] = l; chi[s] = h;
+            used[s] = true;
+        }
+        if (used[s]) {
+            lo = {fminf(lo.x, clo[s].x), fminf(lo.y, clo[s].y), fminf(lo.z, clo[s].z)};
+            hi = {fmaxf(hi.x, chi[s].x), fmaxf(hi.y, chi[s].y), fmaxf(hi.z, chi[s].z)};
+        }
+    }
+    box_lo[i] = lo; box_hi[i] = hi;
+    node_frame(nd, lo, hi);
+    for (int s = 0; s < 8; ++s) {
+        nd.qlox[s] = nd.qloy[s] = nd.qloz[s] = 0;
+        nd.qhix[s] = nd.qhiy[s] = nd.qhiz[s] = 0;
+        if (used[s]) node_quantise_slot(nd, s, clo[s], chi[s]);
+    }
+    nodes[i] = nd;
 }
 
 }  // namespace pb

@@ -30,6 +30,76 @@ static const float* device_texels(void* user, const pb_texture& t) {
     return nullptr;
 }
 
+// EmitterHelper::AddAreaEmitter for one object (world/emitter.cpp:169-243): world-space records of its emissive triangles
+// / its sphere, appended to `emit`; returns how many
+static size_t append_area_emitters(pb_ctx* c, const HostObject& o, const ObjRec& r, std::vector<EmitRec>& emit) {
+    const float select_weight = prep::emitter_weight(o.area_radiance);
+    if (o.sphere) {  // SetSphereAreaEmitter, world/emitter.cpp:224-243
+        EmitRec e{};
+        e.type = EM_SPHERE;
+        const float p0[3] = {0.f, 0.f, 0.f}, p1[3] = {0.f + 1.f, 0.f, 0.f};
+        float ctr[3], px[3];
+        prep::transform_point(r.M, p0, ctr);
+        prep::transform_point(r.M, p1, px);
+        for (int k = 0; k < 3; ++k) e.p0[k] = ctr[k];
+        const float dx = ctr[0] - px[0], dy = ctr[1] - px[1], dz = ctr[2] - px[2];
+        const float radius = sqrtf(dx * dx + dy * dy + dz * dz);
+        e.p1[0] = radius;
+        e.area = 4 * 3.14159265358979323846f * radius * radius;
+        e.radiance = prep::tex_rec(o.area_radiance, device_texels(c, o.area_radiance));
+        e.weight = select_weight * e.area;
+        emit.push_back(e);
+        return 1;
+    }
+    // SetMeshAreaEmitter, world/emitter.cpp:169-222
+    const float* P = c->h_pos.data() + 3ull * o.vert_offset;
+    const float* N = c->h_nrm.data() + 3ull * o.vert_offset;
+    const float* T = c->h_uv.data() + 2ull * o.vert_offset;
+    const uint32_t* I = c->h_idx.data() + 3ull * o.index_offset;
+    for (uint32_t f = 0; f < o.n_tri; ++f) {
+        EmitRec e{};
+        e.type = EM_TRI;
+        float* pp[3] = {e.p0, e.p1, e.p2};
+        float* nn[3] = {e.n0, e.n1, e.n2};
+        float* tt[3] = {e.t0, e.t1, e.t2};
+        for (int k = 0; k < 3; ++k) {
+            const uint32_t vi = I[3 * f + k];
+            prep::transform_point(r.M, P + 3 * vi, pp[k]);
+            prep::transform_normal(r.Minv, N + 3 * vi, nn[k]);
+            tt[k][0] = T[2 * vi]; tt[k][1] = T[2 * vi + 1];
+        }
+        const float ax = e.p1[0] - e.p0[0], ay = e.p1[1] - e.p0[1], az = e.p1[2] - e.p0[2];
+        const float bx = e.p2[0] - e.p0[0], by = e.p2[1] - e.p0[1], bz = e.p2[2] - e.p0[2];
+        const float cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+        e.area = sqrtf(cx * cx + cy * cy + cz * cz) * 0.5f;
+        e.radiance = prep::tex_rec(o.area_radiance, device_texels(c, o.area_radiance));
+        e.weight = select_weight * e.area;
+        emit.push_back(e);
+    }
+    return o.n_tri;
+}
+
+// ComputeProbability (world/emitter.cpp:321-337) over the area emitters + the environment record; leaves `emit` with the
+// environment record appended (slot n_area, type EM_NONE when absent) and the running sums of emitter.h:113-121 in `prefix`
+static void finish_emitter_tables(pb_ctx* c, std::vector<EmitRec>& emit, EmitRec env, std::vector<float>& prefix) {
+    float area_weight_sum = 0.f;
+    for (auto& e : emit) area_weight_sum += e.weight;
+    if (!emit.empty())
+        for (auto& e : emit) e.select_probability = e.weight / area_weight_sum * emit.size();
+    // a scene without any emitter is legal here (the reference would dereference an empty group): no NEE, paths end at
+    // the primary vertex (pb_wavefront.cu has_emitters)
+    const size_t emitter_num = (c->has_env ? 1 : 0) + emit.size();
+    if (emitter_num) {
+        for (auto& e : emit) e.select_probability = e.select_probability / emitter_num;
+        env.select_probability = env.weight / emitter_num;
+    }
+    prefix.assign(emit.size(), 0.f);
+    float sum_p = 0.f;
+    for (size_t i = 0; i < emit.size(); ++i) { prefix[i] = sum_p + emit[i].select_probability; sum_p += emit[i].select_probability; }
+    emit.push_back(env);
+    c->stats.n_emitters = emitter_num;
+}
+
 // World::LoadScene -> RenderObject / EmitterHelper / ComputeProbability, then the device BVH build
 static int commit(pb_ctx* c) {
     cudaSetDevice(c->device);
@@ -70,50 +140,7 @@ static int commit(pb_ctx* c) {
         r.emitter_offset = -1;
         if (o.is_emitter) {
             r.emitter_offset = emitter_offset;
-            const float select_weight = prep::emitter_weight(o.area_radiance);
-            if (o.sphere) {  // SetSphereAreaEmitter, world/emitter.cpp:224-243
-                EmitRec e{};
-                e.type = EM_SPHERE;
-                const float p0[3] = {0.f, 0.f, 0.f}, p1[3] = {0.f + 1.f, 0.f, 0.f};
-                float ctr[3], px[3];
-                prep::transform_point(r.M, p0, ctr);
-                prep::transform_point(r.M, p1, px);
-                for (int k = 0; k < 3; ++k) e.p0[k] = ctr[k];
-                const float dx = ctr[0] - px[0], dy = ctr[1] - px[1], dz = ctr[2] - px[2];
-                const float radius = sqrtf(dx * dx + dy * dy + dz * dz);
-                e.p1[0] = radius;
-                e.area = 4 * 3.14159265358979323846f * radius * radius;
-                e.radiance = prep::tex_rec(o.area_radiance, device_texels(c, o.area_radiance));
-                e.weight = select_weight * e.area;
-                emit.push_back(e);
-                emitter_offset += 1;
-            } else {  // SetMeshAreaEmitter, world/emitter.cpp:169-222
-                const float* P = c->h_pos.data() + 3ull * o.vert_offset;
-                const float* N = c->h_nrm.data() + 3ull * o.vert_offset;
-                const float* T = c->h_uv.data() + 2ull * o.vert_offset;
-                const uint32_t* I = c->h_idx.data() + 3ull * o.index_offset;
-                for (uint32_t f = 0; f < o.n_tri; ++f) {
-                    EmitRec e{};
-                    e.type = EM_TRI;
-                    float* pp[3] = {e.p0, e.p1, e.p2};
-                    float* nn[3] = {e.n0, e.n1, e.n2};
-                    float* tt[3] = {e.t0, e.t1, e.t2};
-                    for (int k = 0; k < 3; ++k) {
-                        const uint32_t vi = I[3 * f + k];
-                        prep::transform_point(r.M, P + 3 * vi, pp[k]);
-                        prep::transform_normal(r.Minv, N + 3 * vi, nn[k]);
-                        tt[k][0] = T[2 * vi]; tt[k][1] = T[2 * vi + 1];
-                    }
-                    const float ax = e.p1[0] - e.p0[0], ay = e.p1[1] - e.p0[1], az = e.p1[2] - e.p0[2];
-                    const float bx = e.p2[0] - e.p0[0], by = e.p2[1] - e.p0[1], bz = e.p2[2] - e.p0[2];
-                    const float cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
-                    e.area = sqrtf(cx * cx + cy * cy + cz * cz) * 0.5f;
-                    e.radiance = prep::tex_rec(o.area_radiance, device_texels(c, o.area_radiance));
-                    e.weight = select_weight * e.area;
-                    emit.push_back(e);
-                }
-                emitter_offset += (int)o.n_tri;
-            }
+            emitter_offset += (int)append_area_emitters(c, o, r, emit);
         }
         prim += r.n_prims;
         c->h_objs.push_back(r);
@@ -186,29 +213,50 @@ static int commit(pb_ctx* c) {
         env.row_cdf = c->d_env_tables; env.col_cdf = c->d_env_tables + (h + 1); env.row_weight = c->d_env_tables + (h + 1) + (w + 1) * h;
         c->has_env = true;
     }
-    // ComputeProbability, world/emitter.cpp:321-337
-    float area_weight_sum = 0.f;
-    for (auto& e : emit) area_weight_sum += e.weight;
-    if (!emit.empty())
-        for (auto& e : emit) e.select_probability = e.weight / area_weight_sum * emit.size();
-    // a scene without any emitter is legal here (the reference would dereference an empty group): no NEE, paths end at
-    // the primary vertex (pb_wavefront.cu has_emitters)
-    const size_t emitter_num = (c->has_env ? 1 : 0) + emit.size();
-    if (emitter_num) {
-        for (auto& e : emit) e.select_probability = e.select_probability / emitter_num;
-        env.select_probability = env.weight / emitter_num;
-    }
-    std::vector<float> prefix(emit.size());
-    float sum_p = 0.f;
-    for (size_t i = 0; i < emit.size(); ++i) { prefix[i] = sum_p + emit[i].select_probability; sum_p += emit[i].select_probability; }
-    emit.push_back(env);  // slot n_area_emitters holds the env emitter (type EM_NONE when absent)
+    c->h_env_rec = env;
+    std::vector<float> prefix;
+    finish_emitter_tables(c, emit, env, prefix);
     if (upload(c, &c->d_emit, emit) || upload(c, &c->d_emit_prefix, prefix)) return PB_ERR_CUDA;
 
-    c->stats.n_prims = prim; c->stats.n_nodes = c->n_nodes; c->stats.n_emitters = emitter_num;
+    c->stats.n_prims = prim; c->stats.n_nodes = c->n_nodes;
     c->stats.n_objects = (uint32_t)c->h_objs.size(); c->stats.bvh_depth = c->bvh_levels;
     c->stats.build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     c->committed = true;
     ++c->scene_epoch;
+    c->refits = 0; c->rebuilds = 0;
+    return PB_OK;
+}
+
+// pb_update_instance without a rebuild: new object record, refit (pb_build.cu refit_object), emitter tables rewritten in
+// place.  *done = false -> the caller falls back to commit().
+static int update_by_refit(pb_ctx* c, uint32_t object, bool* done) {
+    *done = false;
+    if (!c->committed || !c->allow_refit || object >= c->h_objs.size()) return PB_OK;
+    cudaSetDevice(c->device);
+    int rc = wavefront_wait(c);          // renders in flight still traverse the old boxes
+    if (rc != PB_OK) return rc;
+    auto t0 = std::chrono::steady_clock::now();
+    const uint32_t launches0 = c->stats.kernel_launches;
+    ObjRec& r = c->h_objs[object];
+    memcpy(r.M, c->objects[object].M, 48);
+    invert_affine(r.M, r.Minv);
+    PB_CUDA_TRY(c, cudaMemcpyAsync(c->d_objs + object, &r, sizeof(ObjRec), cudaMemcpyHostToDevice, c->stream));
+    rc = refit_object(c, object, done, c->stream);
+    if (rc != PB_OK || !*done) return rc;
+    if (c->objects[object].is_emitter) {   // ResetAreaEmitter + ComputeProbability (world.cpp:49-52): same count, same buffers
+        std::vector<EmitRec> emit;
+        for (size_t oi = 0; oi < c->objects.size(); ++oi)
+            if (c->objects[oi].is_emitter) append_area_emitters(c, c->objects[oi], c->h_objs[oi], emit);
+        if (emit.size() != c->n_area_emitters) { *done = false; return PB_OK; }
+        std::vector<float> prefix;
+        finish_emitter_tables(c, emit, c->h_env_rec, prefix);
+        PB_CUDA_TRY(c, cudaMemcpyAsync(c->d_emit, emit.data(), emit.size() * sizeof(EmitRec), cudaMemcpyHostToDevice, c->stream));
+        if (!prefix.empty()) PB_CUDA_TRY(c, cudaMemcpyAsync(c->d_emit_prefix, prefix.data(), prefix.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+        PB_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    }
+    c->stats.build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->stats.kernel_launches -= launches0;      // launches of this call, like commit() reports them
+    ++c->refits;
     return PB_OK;
 }
 
@@ -223,8 +271,17 @@ PB_API int pb_scene_commit(pb_ctx* c) {
 PB_API int pb_update_instance(pb_ctx* c, uint32_t object, const float to_world[12]) {
     if (!c) return PB_ERR_INVALID;
     PB_REQUIRE(object < c->objects.size(), "object id out of range");
+    PB_REQUIRE(to_world != nullptr, "null transform");
     memcpy(c->objects[object].M, to_world, 48);
-    return commit(c);   // LBVH rebuild on device is this framework's IAS::Update
+    // IAS::Update (world/ias_manager.cpp:116-151): refit in place; a rebuild only when the move changes the scene box enough
+    // to change delta (the padding every accepted hit is defined against), or before the first commit
+    bool done = false;
+    int rc = update_by_refit(c, object, &done);
+    if (rc != PB_OK) return rc;
+    if (done) return PB_OK;
+    rc = commit(c);
+    if (rc == PB_OK) c->rebuilds = 1;
+    return rc;
 }
 
 }  // extern "C"

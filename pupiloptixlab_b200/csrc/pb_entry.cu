@@ -227,6 +227,7 @@ PB_API int pb_get_stats(pb_ctx* c, pb_stats* out) {
     int rc = wavefront_wait(c);
     if (rc == PB_OK) rc = comm_poll(c);
     if (rc != PB_OK) return rc;
+    c->stats.refits = c->refits; c->stats.rebuilds = c->rebuilds;
     *out = c->stats;
     return PB_OK;
 }

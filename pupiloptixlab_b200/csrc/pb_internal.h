@@ -55,6 +55,7 @@ struct pb_ctx {
     float* d_emit_prefix = nullptr;      // running sums of select_probability (emitter.h:110-121)
     float* d_env_tables = nullptr;
     uint32_t n_area_emitters = 0;
+    pb::EmitRec h_env_rec{};             // the environment record of the last commit (table pointers included), reused by refits
     bool has_env = false;
     std::vector<pb::ObjRec> h_objs;
     std::vector<float*> d_bitmaps;       // device copies of `bitmaps` (same order), RGBA float, sampled in software (pb_shade.cuh)
@@ -65,6 +66,14 @@ struct pb_ctx {
     uint32_t n_nodes = 0, n_prims = 0, bvh_levels = 0;
     float delta = 0.f;
     pb::V3 scene_lo{}, scene_hi{};
+    // ---- refit state (pb_update_instance without a rebuild): BFS level boundaries of d_nodes, one exact (lo, hi) box
+    // per node, the exact world box of every object (the scene box = their union decides delta)
+    std::vector<uint32_t> level_first;   // level l = nodes [level_first[l], level_first[l + 1])
+    pb::V3* d_node_lo = nullptr; pb::V3* d_node_hi = nullptr;
+    std::vector<pb::V3> h_obj_lo, h_obj_hi;
+    uint32_t* d_obj_box = nullptr;       // 6 ordered uints per object (scratch of the box reductions)
+    bool allow_refit = true;             // PB_NO_REFIT=1: every pb_update_instance rebuilds (A/B, tests)
+    uint32_t refits = 0, rebuilds = 0;   // how pb_update_instance was served since the last commit
 
     // ---- scratch
     unsigned long long* d_counters = nullptr;   // [0] ray fetch cursor, [1..3] visit counters
@@ -100,7 +109,10 @@ struct pb_ctx {
 namespace pb {
 // pb_build.cu
 int build_bvh(pb_ctx* c, const PrimRec* d_prims_in, uint32_t n, cudaStream_t s);
-int make_world_prims(pb_ctx* c, PrimRec* d_out, cudaStream_t s);   // also computes scene box + delta
+int make_world_prims(pb_ctx* c, PrimRec* d_out, cudaStream_t s);   // also computes scene box + delta + per-object boxes
+// refit after object `object`'s transform changed (d_objs already holds the new matrices).  *done = false: the scene box
+// (and with it delta, part of the intersection contract) changed, the caller must rebuild
+int refit_object(pb_ctx* c, uint32_t object, bool* done, cudaStream_t s);
 // pb_trace.cu
 int trace_rays(pb_ctx* c, const pb_ray* d_rays, uint64_t n, pb_hit* d_hits, uint8_t* d_occ, bool any, bool counted, cudaStream_t s);
 // pb_wavefront.cu

@@ -27,6 +27,8 @@ struct HS {
     float delta = 0;
     uint32_t levels = 0;
     TraceCounters cnt{};
+    std::vector<uint32_t> level_first;      // BFS level boundaries of `nodes`
+    std::vector<V3> box_lo, box_hi;         // per-node boxes of the refit
 };
 
 extern "C" {
@@ -97,8 +99,10 @@ HS* hs_create(const float* pos, uint32_t n_vert, const uint32_t* idx, uint32_t n
     std::vector<WorkItem> work(1), next;
     work[0] = {n == 1 ? (0u | kLeafFlag) : 0u, 0u};
     uint32_t wide_count = 1, prim_cursor = 0;
+    h->level_first.assign(1, 0u);
     while (!work.empty()) {
         ++h->levels;
+        h->level_first.push_back(wide_count);
         uint32_t nw = (uint32_t)work.size();
         std::vector<uint32_t> plan(8 * (size_t)nw), ci(nw), cp(nw);
         next.assign(8 * (size_t)nw, WorkItem{0, 0});
@@ -114,6 +118,7 @@ HS* hs_create(const float* pos, uint32_t n_vert, const uint32_t* idx, uint32_t n
         work.swap(next);
     }
     h->nodes.resize(wide_count);
+    h->level_first.push_back(wide_count);
     if (prim_cursor != n) fprintf(stderr, "hostsim: leaf prim count %u != %u\n", prim_cursor, n);
     return h;
 }
@@ -153,6 +158,33 @@ void hs_trace_any(HS* h, const float* rays, uint64_t n, uint8_t* occ) {
         traverse<true, true>(sc, {r[0], r[1], r[2]}, {r[4], r[5], r[6]}, r[3], r[7], hit, st, &h->cnt);
         occ[i] = hit.prim != 0xFFFFFFFFu;
     }
+}
+// pb_update_instance's refit path (pb_build.cu refit_object) on the CPU: new transform of object `obj`, its leaf records
+// rewritten, every level refitted bottom-up with the same PB_HD body.  Returns 0, or 1 when delta would change (the
+// product rebuilds then).
+int hs_move_object(HS* h, uint32_t obj, const float* M) {
+    if (obj >= h->objs.size()) return 2;
+    memcpy(h->objs[obj].M, M, 48);
+    invert_affine(h->objs[obj].M, h->objs[obj].Minv);
+    const uint32_t n = (uint32_t)h->prims_out.size();
+    SceneGeom g{h->pos.data(), nullptr, nullptr, h->idx.data(), h->objs.data(), (uint32_t)h->objs.size(), n, nullptr};
+    for (uint32_t i = 0; i < n; ++i)
+        if (f2u(h->prims_out[i].b.w) == obj) h->prims_out[i] = make_prim(g, f2u(h->prims_out[i].a.w));
+    const float fm = 3.402823466e38f;
+    V3 slo = v3(fm), shi = v3(-fm);
+    for (uint32_t i = 0; i < n; ++i) {
+        V3 lo, hi;
+        prim_bbox(h->prims_out[i], lo, hi);
+        slo = {fminf(slo.x, lo.x), fminf(slo.y, lo.y), fminf(slo.z, lo.z)};
+        shi = {fmaxf(shi.x, hi.x), fmaxf(shi.y, hi.y), fmaxf(shi.z, hi.z)};
+    }
+    const float delta = fmaxf(fmaxf(shi.x - slo.x, shi.y - slo.y), shi.z - slo.z) * (1.0f / 262144.0f);
+    if (f2u(delta) != f2u(h->delta)) return 1;
+    h->box_lo.resize(h->nodes.size()); h->box_hi.resize(h->nodes.size());
+    for (size_t l = h->level_first.size() - 1; l-- > 0;)
+        for (uint32_t i = h->level_first[l]; i < h->level_first[l + 1]; ++i)
+            refit_wide_node(h->nodes.data(), h->prims_out.data(), h->box_lo.data(), h->box_hi.data(), h->delta, i);
+    return 0;
 }
 // the committed tree as pb_export_bvh hands it out: 80-byte nodes + 48-byte primitive records in leaf order
 void hs_export(HS* h, void* nodes80, void* prims48) {

@@ -171,9 +171,13 @@ def test_async_renders_fold_into_one_wait(api):
     assert np.array_equal(acc.numpy().view(np.uint32), ref.view(np.uint32))
 
 
-def test_update_instance_rebuilds(api, oracle_api):
+@pytest.mark.parametrize("refit", [True, False])
+def test_update_instance_rebuilds(api, oracle_api, refit, monkeypatch):
     """pb_update_instance (IAS::Update semantics, world/ias_manager.cpp:116-151): moving one object changes the
-    hits exactly as the oracle's rebuilt scene does."""
+    hits exactly as the oracle's rebuilt scene does — by the in-place refit (default) and by the full rebuild
+    (PB_NO_REFIT=1) alike."""
+    if not refit:
+        monkeypatch.setenv("PB_NO_REFIT", "1")
     from tests import util_scenes as U
     w = h = 96
     res = {}
@@ -184,6 +188,9 @@ def test_update_instance_rebuilds(api, oracle_api):
         m[:3, :3] *= 0.3
         m[:3, 3] = (-0.2, 0.9, 0.1)
         ctx.update_instance(obj, m[:3])
+        if name == "g":
+            st = ctx.stats()
+            assert (st["refits"], st["rebuilds"]) == ((1, 0) if refit else (0, 1))
         rays = U.random_rays(50000, 77)
         rays["ox"], rays["oy"], rays["oz"] = 0.0, 1.0, 3.0
         res[name] = (ctx.trace_closest(rays), ctx.render(w, h, 4, 0, 2)[0])
@@ -221,3 +228,40 @@ def test_c2_full_size_matches_oracle(api, oracle_api):
     assert np.array_equal(sg[..., 3], so[..., 3])
     assert rel_ok_fraction(sg[..., :3], so[..., :3]) >= PIXEL_FRACTION
     assert rel_ok_fraction(ag, ao) >= PIXEL_FRACTION and rel_ok_fraction(ng, no) >= PIXEL_FRACTION
+
+
+def test_update_instance_of_lights_and_meshes(api, oracle_api):
+    """Refit with the emitter tables rewritten in place: an emissive rectangle (two triangle emitters) and the emissive
+    sphere are moved and rescaled (areas, weights and select probabilities change), a mesh is rotated; a move far outside
+    the room changes the scene extent and is served by the rebuild.  Renders and hits equal the oracle's edited scene."""
+    from tests import util_scenes as U
+    w = h = 96
+    g, o = capi.Context(api), pyoracle.OracleContext(oracle_api)
+    info = scenes.cornell_box(g, w, h, "materials")
+    scenes.cornell_box(o, w, h, "materials")
+    objs = info["objects"]
+    light = scenes.CORNELL["Light"][1].copy()
+    light[:3, :3] *= 1.4
+    light[1, 3] -= 0.15
+    edits = [(objs["Light"], light), (objs["bulb"], scenes.translate(-0.5, 1.2, 0.3) @ scenes.scale(0.1, 0.1, 0.1)),
+             (objs["TallBox"], scenes.translate(0.05, 0.0, 0.1) @ scenes.CORNELL["TallBox"][1] @ scenes.rotate(0, 1, 0, 20)),
+             (objs["sphere2"], scenes.translate(0.2, 0.6, 0.2) @ scenes.rotate(1, 0, 1, 35) @ scenes.scale(0.3, 0.12, 0.2))]
+    rays = U.random_rays(40000, 5)
+    rays["ox"], rays["oy"], rays["oz"] = 0.0, 1.0, 3.0
+    for k, (obj, m) in enumerate(edits):
+        for ctx in (g, o):
+            ctx.update_instance(obj, np.asarray(m, np.float32)[:3])
+        st = g.stats()
+        assert st["refits"] == k + 1 and st["rebuilds"] == 0, st
+        hg, ho = g.trace_closest(rays), o.trace_closest(rays)
+        assert np.array_equal(hg["prim"], ho["prim"]) and np.array_equal(hg["t"].view(np.uint32), ho["t"].view(np.uint32))
+        sg, so = g.render(w, h, 5, 0, 4)[0], o.render(w, h, 5, 0, 4)[0]
+        assert rel_ok_fraction(sg[..., :3], so[..., :3]) >= PIXEL_FRACTION, f"edit {k}"
+        assert g.stats()["n_emitters"] == o.stats()["n_emitters"] == 3
+    far = scenes.translate(0.0, 1.0, 40.0) @ scenes.scale(0.2, 0.2, 0.2)
+    for ctx in (g, o):
+        ctx.update_instance(objs["sphere0"], far[:3].astype(np.float32))
+    st = g.stats()
+    assert st["rebuilds"] == 1 and st["refits"] == 0          # counters restart with the commit
+    sg, so = g.render(w, h, 5, 0, 2)[0], o.render(w, h, 5, 0, 2)[0]
+    assert rel_ok_fraction(sg[..., :3], so[..., :3]) >= PIXEL_FRACTION
