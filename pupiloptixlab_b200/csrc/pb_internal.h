@@ -81,7 +81,9 @@ struct pb_ctx {
     int sm_count = 148;
     uint32_t leaf_max = 2;               // primitives per leaf slot (PB_LEAF_MAX, 1..3)
     uint32_t bottom_max = 8;             // BVH collapse: subtrees up to this size become one wide node (PB_BOTTOM_MAX)
-    uint32_t prim_iters = 0xFFFFFFFFu;   // PB_PRIM_ITERS
+    uint32_t prim_iters = 2u;            // primitives a lane tests per primitive phase (PB_PRIM_ITERS).  Round 2, C4, same box:
+                                         // unlimited 520.6, 1: 521.4, 2: 529.2 Msamples/s (round 1's optimum was unlimited: the
+                                         // sphere records were dependent fetches then)
     uint32_t prim_batch = 8;             // lanes holding primitives before a warp runs its primitive tests (PB_PRIM_BATCH)
     uint32_t refill = 20;                // dynamic-fetch threshold (PB_REFILL overrides, tuning only)
     pb_stats stats{};

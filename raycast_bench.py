@@ -61,7 +61,8 @@ def main():
     ap.add_argument("--orders", action="store_true", help="also time the incoherent set in primary-pixel order and binned by direction octant")
     ap.add_argument("--no-sorted", action="store_true", help="skip the origin-Morton-sorted variant of the incoherent set")
     ap.add_argument("--spheres", type=int, default=0)
-    ap.add_argument("--check", type=int, default=0)
+    ap.add_argument("--check", type=int, default=0, help="rays of each set compared with the oracle's BVH traversal (bit-exact ids and t)")
+    ap.add_argument("--brute", type=int, default=0, help="rays of each set compared with the oracle's brute-force loop over all primitives")
     ap.add_argument("--reps", type=int, default=5)
     args = ap.parse_args()
     import torch
@@ -139,13 +140,31 @@ def one_mesh(args, mesh_name, prim, api, capi, scenes, torch, dev, stream, peak)
         from oracle import pyoracle
         o = pyoracle.OracleContext(pyoracle.load())
         scenes.bench_scene(o, n, args.spheres, 1920, 1080, patchwork=False, mesh=mesh)
+        bvh = o.import_cwbvh(g)       # the committed 8-wide BVH, read by the oracle (structure + leaf records verified)
         for name, rays, got in (("coherent", prim, hp), ("incoherent", inc, hi)):
             sel = np.random.RandomState(9).randint(0, len(rays), args.check)
+            t_o = time.time()
             want = o.trace_closest(rays[sel])
+            t_o = time.time() - t_o
             bad = int((want["prim"] != got["prim"][sel]).sum())
             hit = want["prim"] != capi.MISS
             bad_t = int((want["t"][hit].view(np.uint32) != got["t"][sel][hit].view(np.uint32)).sum())
-            print(json.dumps({"check": name, "mesh": mesh_name, "rays": args.check, "id_mismatches": bad, "t_mismatches": bad_t, "hit_fraction": float(hit.mean())}), flush=True)
+            # algorithmic bytes from the ORACLE's ordered, t-culled traversal of that BVH (a 10^6-ray subset)
+            sub = rays[sel[:1_000_000]]
+            cw, cnt = o.trace_cwbvh(sub)
+            b_orc = 48.0 + (80.0 * cnt["nodes"] + 48.0 * cnt["tris"] + 32.0 * cnt["spheres"]) / len(sub)
+            print(json.dumps({"check": name, "mesh": mesh_name, "rays": args.check, "id_mismatches": bad, "t_mismatches": bad_t, "hit_fraction": float(hit.mean()),
+                              "oracle_mrays_per_s": args.check / t_o / 1e6,
+                              "oracle_ordered_traversal": {"rays": len(sub), "nodes_per_ray": cnt["nodes"] / len(sub), "tris_per_ray": cnt["tris"] / len(sub),
+                                                           "spheres_per_ray": cnt["spheres"] / len(sub), "bytes_per_ray": b_orc,
+                                                           "id_mismatches_vs_own_bvh": int((cw["prim"] != want["prim"][:len(sub)]).sum())},
+                              "bvh": bvh}), flush=True)
+        if args.brute:      # ground truth: O(N) loop over every primitive, a small subset
+            for name, rays, got in (("coherent", prim, hp), ("incoherent", inc, hi)):
+                sel = np.random.RandomState(10).randint(0, len(rays), args.brute)
+                want = o.trace_closest_brute(rays[sel])
+                print(json.dumps({"check": name + " vs brute force", "mesh": mesh_name, "rays": args.brute,
+                                  "id_mismatches": int((want["prim"] != got["prim"][sel]).sum())}), flush=True)
         del o
     del g
 
