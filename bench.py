@@ -412,9 +412,14 @@ def product_main(args):
             g.render_dev(capi.RenderParams(WIDTH, HEIGHT, MAX_DEPTH, i_chk * S * N, S * N, 1, capi.RENDER_CLEAR, 0), d_one.data_ptr(), 0, 0, sp)
             torch.cuda.synchronize(dev)
             a, b = d_sum[..., :3].double(), d_one[..., :3].double()
+            # the reference has no NaN / Inf guard: a non-finite pixel must be non-finite on both sides
+            fin = torch.isfinite(a).all(-1) & torch.isfinite(b).all(-1)
+            nonfinite_equal = bool(torch.equal(torch.isfinite(a), torch.isfinite(b)))
+            a = torch.where(fin[..., None], a, torch.zeros_like(a)); b = torch.where(fin[..., None], b, torch.zeros_like(b))
             rel = ((a - b).abs() / (b.abs() + 1e-3)).amax(-1)
             parity = {"frames": S * N, "step": i_chk, "against": "the same frames rendered by rank 0 alone (sample_stride 1)",
                       "counts_equal": bool(torch.equal(d_sum[..., 3], d_one[..., 3])) and float(d_one[0, 0, 3]) == S * N,
+                      "non_finite_pixels": int((~fin).sum()), "non_finite_equal": nonfinite_equal,
                       "max_rel": float(rel.max()), "pixels_within_1e-5": float((rel <= 1e-5).double().mean()),
                       "film_mean_ratio": float(a.mean() / b.mean()),
                       "note": "frames are bit-identical on every GPU; the only difference is the order of the float additions (per-rank sums, then the reduce)"}
