@@ -204,6 +204,16 @@ PB_API int pb_trace_any(pb_ctx* ctx, const pb_ray* rays, uint64_t n, uint8_t* oc
 PB_API int pb_trace_closest_counted(pb_ctx* ctx, const pb_ray* rays, uint64_t n, pb_hit* hits, int host, void* cuda_stream);
 PB_API int pb_trace_any_counted(pb_ctx* ctx, const pb_ray* rays, uint64_t n, uint8_t* occluded, int host, void* cuda_stream);
 
+/* ---- allocation-free closest hit.  NO COUNTERPART IN THE REFERENCE: added at the request of this run's operators for
+ * callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid it).  Same result as pb_trace_closest,
+ * bit for bit; it allocates nothing (no cudaMalloc / cudaFree / event creation): the kernel's scratch — ray cursor and
+ * counters, and for host != 0 the device staging of rays and hits — is a file-scope device array of
+ * 256 B + 48 B x PB_STATIC_TRACE_MAX_RAYS (12.0 MiB) that every GPU loading the library holds until the process exits.
+ * n > PB_STATIC_TRACE_MAX_RAYS is refused with PB_ERR_LIMIT.  Synchronous.  All calls on a device share that array:
+ * calls that overlap on the GPU (other streams / threads) race — serialise them.                                       */
+#define PB_STATIC_TRACE_MAX_RAYS 262144u
+PB_API int pb_trace_closest_static(pb_ctx* ctx, const pb_ray* rays, uint64_t n, pb_hit* hits, int host, void* cuda_stream);
+
 /* ---- render.  Replaces PTPass::OnRun → optix::Pass::Run → optixLaunch(w,h,1) repeated
  * sample_count times (path_tracer/pt_pass.cpp:39-57, framework/optix/pass.h:69-87).
  * accum_sum_rgba: w*h float4, receives SUMS of per-frame radiance in .xyz and the number of frames

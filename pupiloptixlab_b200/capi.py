@@ -390,6 +390,7 @@ def load() -> Api:
         api._f("trace_closest_counted", i32, [vp, vp, u64, vp, i32, vp])
         api._f("trace_any_counted", i32, [vp, vp, u64, vp, i32, vp])
         api._f("export_bvh", i32, [vp, vp, C.POINTER(u64), vp, C.POINTER(u64)])
+        api._f("trace_closest_static", i32, [vp, vp, u64, vp, i32, vp])
         api._f("comm_unique_id", i32, [vp])
         api._f("comm_init_rank", i32, [vp, vp, i32, i32])
         api._f("comm_info", i32, [vp, C.POINTER(i32), C.POINTER(i32)])

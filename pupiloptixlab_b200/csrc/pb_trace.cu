@@ -4,6 +4,8 @@
 // Persistent kernel: grid = SM count x resident CTAs, 128 threads per CTA.  A warp claims 32
 // consecutive rays at a time from a global cursor (one atomicAdd per warp), so lanes of a warp
 // read rays / write hits as contiguous 128-bit vectors.  Traversal stack head in shared memory.
+#include <mutex>
+
 #include "pb_internal.h"
 #include "pb_trace_loop.cuh"
 
@@ -80,4 +82,71 @@ int trace_rays(pb_ctx* c, const pb_ray* d_rays, uint64_t n_total, pb_hit* d_hits
     return PB_OK;
 }
 
+// ---- allocation-free closest-hit entry point (pb_trace_closest_static, include/pupil_b200.h) -------------------------------
+// The scratch of k_trace - the ray cursor + visit counters, and for host buffers the device staging of rays and hits that
+// pb_trace_closest cudaMallocs per call - lives in ONE file-scope device array of fixed size.  Every GPU that loads the
+// library holds it (256 B + 48 B x PB_STATIC_TRACE_MAX_RAYS = 12.0 MiB) until the process exits.
+//   [0, 256)                         cursor + counters (cleared at the head of every call)
+//   [256, 256 + 32 MAX)              pb_ray staging (host-buffer calls)
+//   [256 + 32 MAX, 256 + 48 MAX)     pb_hit staging (host-buffer calls)
+// All calls on a device share the array and it keeps the last call's contents: two calls that overlap on the GPU
+// (different streams, or asynchronous use) race on the cursor and on the staging area.  The entry point is synchronous.
+static __device__ __align__(256) unsigned char g_static_scratch[256 + 48ull * PB_STATIC_TRACE_MAX_RAYS];
+
+namespace {
+// In host code `g_static_scratch` is only the host-side shadow of the symbol, not a device address: each device's real
+// address is taken once, with that device current, by cudaGetSymbolAddress.
+std::mutex g_static_mutex;
+unsigned char* g_static_ptr[64] = {};
+bool g_static_known[64] = {};
+
+cudaError_t static_scratch_for(int device, unsigned char** out) {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    if (!g_static_known[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaSetDevice(device);
+        if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_static_ptr[device] = static_cast<unsigned char*>(p);
+        g_static_known[device] = true;
+    }
+    *out = g_static_ptr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
 }  // namespace pb
+
+extern "C" PB_API int pb_trace_closest_static(pb_ctx* c, const pb_ray* rays, uint64_t n, pb_hit* hits, int host, void* stream) {
+    using namespace pb;
+    if (!c) return PB_ERR_INVALID;
+    if (!c->committed) { c->err = "scene not committed"; return PB_ERR_NOT_COMMITTED; }
+    if (n > (uint64_t)PB_STATIC_TRACE_MAX_RAYS) {
+        c->err = "pb_trace_closest_static: " + std::to_string(n) + " rays exceed the static scratch (PB_STATIC_TRACE_MAX_RAYS = " +
+                 std::to_string((unsigned long long)PB_STATIC_TRACE_MAX_RAYS) + "); split the batch or use pb_trace_closest";
+        return PB_ERR_LIMIT;
+    }
+    if (n == 0) return PB_OK;
+    if (!rays || !hits) { c->err = "null ray / result pointer"; return PB_ERR_INVALID; }
+    unsigned char* base = nullptr;
+    PB_CUDA_TRY(c, static_scratch_for(c->device, &base));
+    PB_CUDA_TRY(c, cudaSetDevice(c->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    unsigned long long* counters = reinterpret_cast<unsigned long long*>(base);
+    pb_ray* d_rays = reinterpret_cast<pb_ray*>(base + 256);
+    pb_hit* d_hits = reinterpret_cast<pb_hit*>(base + 256 + 32ull * PB_STATIC_TRACE_MAX_RAYS);
+    PB_CUDA_TRY(c, cudaMemsetAsync(counters, 0, 256, s));                       // the cursor must start at zero
+    if (host) PB_CUDA_TRY(c, cudaMemcpyAsync(d_rays, rays, n * sizeof(pb_ray), cudaMemcpyHostToDevice, s));
+    const float4* r = reinterpret_cast<const float4*>(host ? d_rays : rays);
+    float4* h = reinterpret_cast<float4*>(host ? d_hits : hits);
+    const unsigned long long want = (n + kTraceThreads - 1) / kTraceThreads;
+    const unsigned grid = (unsigned)std::min<unsigned long long>(want, (unsigned long long)c->sm_count * 8ull);
+    k_trace<false, false><<<grid, kTraceThreads, 0, s>>>(c->trace_scene(), r, (uint32_t)n, h, nullptr, counters);
+    PB_CUDA_TRY(c, cudaGetLastError());
+    if (host) PB_CUDA_TRY(c, cudaMemcpyAsync(hits, d_hits, n * sizeof(pb_hit), cudaMemcpyDeviceToHost, s));
+    PB_CUDA_TRY(c, cudaStreamSynchronize(s));
+    c->stats.rays_closest = n;
+    c->stats.kernel_launches += 1;
+    return PB_OK;
+}

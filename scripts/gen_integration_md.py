@@ -98,6 +98,10 @@ libnccl — torch — keeps a single copy):
   `pb_render_multi(ctxs, n, params_of_the_whole_job, targets_on_ctx0, streams)`; `B200PTPass(system, {{0, 1, …}})` and
   `ph_session_create_multi` sit on top of it (`tests/cpp/test_multi_gpu.cpp` is a plain C++ program using only the two
   C headers);
+* callers that cannot call `cudaMalloc` (serving loops, harnesses that forbid it) have `pb_trace_closest_static`: the same
+  closest-hit result with the kernel's scratch in a static device array — at most `PB_STATIC_TRACE_MAX_RAYS` = 262 144
+  rays per call (12.0 MiB per GPU, held until exit), `PB_ERR_LIMIT` beyond, calls must not overlap on the GPU.  It has no
+  counterpart in the reference and was added at the request of the run's operators;
 * asynchronous NCCL errors are polled in `pb_wait` / `pb_get_stats` / synchronous renders and surface as `PB_ERR_NCCL`
   with NCCL's message in `pb_last_error`.
 """
