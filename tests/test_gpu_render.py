@@ -244,7 +244,7 @@ def test_update_instance_of_lights_and_meshes(api, oracle_api):
     light[:3, :3] *= 1.4
     light[1, 3] -= 0.15
     edits = [(objs["Light"], light), (objs["bulb"], scenes.translate(-0.5, 1.2, 0.3) @ scenes.scale(0.1, 0.1, 0.1)),
-             (objs["TallBox"], scenes.translate(0.05, 0.0, 0.1) @ scenes.CORNELL["TallBox"][1] @ scenes.rotate(0, 1, 0, 20)),
+             (objs["TallBox"], scenes.translate(0.05, 0.0, 0.1) @ scenes.CORNELL["TallBox"][1] @ scenes.rotate(0, 0, 1, 20)),   # about the box's height axis (object z): stays inside the room
              (objs["sphere2"], scenes.translate(0.2, 0.6, 0.2) @ scenes.rotate(1, 0, 1, 35) @ scenes.scale(0.3, 0.12, 0.2))]
     rays = U.random_rays(40000, 5)
     rays["ox"], rays["oy"], rays["oz"] = 0.0, 1.0, 3.0
