@@ -35,6 +35,9 @@ PB_API int pb_create(pb_ctx** out, int device) {
     if (const char* e = getenv("PB_PRIM_BATCH")) { int v = atoi(e); if (v >= 1 && v <= 32) c->prim_batch = (uint32_t)v; }
     if (const char* e = getenv("PB_LEAF_MAX")) { int v = atoi(e); if (v >= 1 && v <= 3) c->leaf_max = (uint32_t)v; }
     if (const char* e = getenv("PB_BOTTOM_MAX")) { int v = atoi(e); if (v >= 0 && v <= 24) c->bottom_max = (uint32_t)v; }
+    if (const char* e = getenv("PB_PRIM_ITERS_ANY")) { int v = atoi(e); if (v >= 1) c->prim_iters_any = (uint32_t)v; }
+    if (const char* e = getenv("PB_PRIM_BATCH_ANY")) { int v = atoi(e); if (v >= 1 && v <= 32) c->prim_batch_any = (uint32_t)v; }
+    if (const char* e = getenv("PB_REFILL_ANY")) { int v = atoi(e); if (v >= 1 && v <= 32) c->refill_any = (uint32_t)v; }
     if (getenv("PB_NO_GRAPH")) c->use_graphs = false;
     if (getenv("PB_NO_REFIT")) c->allow_refit = false;
     if (const char* e = getenv("PB_REFILL")) { int v = atoi(e); if (v >= 1 && v <= 32) c->refill = (uint32_t)v; }

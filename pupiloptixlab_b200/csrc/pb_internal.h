@@ -94,6 +94,16 @@ struct pb_ctx {
     float* d_reduce = nullptr;           // w*h float4: this rank's frames of one PB_RENDER_REDUCE call, reduced in place
     size_t reduce_px = 0;
 
+    // the any-hit kernel (k_connect) ends a ray at its first accepted hit, so its batching knobs are tuned separately
+    // (PB_PRIM_BATCH_ANY / PB_PRIM_ITERS_ANY / PB_REFILL_ANY; 0 = the closest-hit value)
+    uint32_t prim_iters_any = 0, prim_batch_any = 0, refill_any = 0;
+    pb::TraceScene trace_scene_any() const {
+        pb::TraceScene t = trace_scene();
+        if (refill_any) t.refill = refill_any;
+        if (prim_batch_any) t.prim_batch = prim_batch_any;
+        if (prim_iters_any) t.prim_iters = prim_iters_any;
+        return t;
+    }
     pb::TraceScene trace_scene() const {
         return pb::TraceScene{reinterpret_cast<const pb::U4*>(d_nodes), reinterpret_cast<const pb::V4*>(d_prims), d_objs, delta, n_nodes, refill, prim_batch, 0x47000000u, prim_iters};
     }

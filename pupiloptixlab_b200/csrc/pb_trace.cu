@@ -50,7 +50,7 @@ k_trace(TraceScene sc, const float4* __restrict__ rays, uint32_t n, float4* __re
 
 int trace_rays(pb_ctx* c, const pb_ray* d_rays, uint64_t n_total, pb_hit* d_hits, uint8_t* d_occ, bool any, bool counted, cudaStream_t s) {
     if (n_total == 0) return PB_OK;
-    const TraceScene sc = c->trace_scene();
+    const TraceScene sc = any ? c->trace_scene_any() : c->trace_scene();
     unsigned long long visits[3] = {0ull, 0ull, 0ull};
     // the ray cursor is 32-bit: batches of at most 2^30 rays per launch
     for (uint64_t first = 0; first < n_total; first += (1ull << 30)) {

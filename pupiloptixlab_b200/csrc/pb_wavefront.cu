@@ -107,6 +107,7 @@ struct Wavefront {
 
 struct WfScene {
     TraceScene ts;
+    TraceScene ts_any;       // k_connect's copy (own batching knobs)
     SceneGeom geom;
     const MatRec* mats;
     EmitterTable em;
@@ -256,7 +257,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfS
     const uint32_t n = s.cnt[C_SHADOW];
     TraceCounters tc = {0ull, 0ull, 0ull};
     ConnectIO io{s, n};
-    trace_loop<true, COUNT>(sc.ts, io, st, &s.cnt[C_CUR_CON], n, sc.ts.refill, tc);
+    trace_loop<true, COUNT>(sc.ts_any, io, st, &s.cnt[C_CUR_CON], n, sc.ts_any.refill, tc);
     if (COUNT) { atomicAdd(&s.totals[5], tc.nodes); atomicAdd(&s.totals[6], tc.tris); atomicAdd(&s.totals[7], tc.spheres); }
 }
 
@@ -575,6 +576,7 @@ int wavefront_render(pb_ctx* c, const pb_render_params* p, float* d_sum, float* 
     const WfState& st = c->wf->st;
     WfScene sc{};
     sc.ts = c->trace_scene();
+    sc.ts_any = c->trace_scene_any();
     sc.geom = SceneGeom{c->d_pos, c->d_nrm, c->d_uv, c->d_idx, c->d_objs, (uint32_t)c->h_objs.size(), c->n_prims, c->d_trishade};
     sc.mats = c->d_mats;
     sc.em = EmitterTable{c->d_emit, c->d_emit_prefix, c->n_area_emitters};
