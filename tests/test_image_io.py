@@ -306,3 +306,33 @@ def test_xml_bitmap_texture_and_envmap(tmp_path, oracle_api):
     rb = b.render(64, 48, 5, 0, 4)[0]
     err = np.abs(ra - rb)[..., :3] / (np.abs(rb[..., :3]) + 1e-3)
     assert (err.max(-1) <= 1e-3).mean() >= 0.99
+
+
+def test_crafted_headers_are_refused_not_read_past_the_end(tmp_path):
+    """the decoders run on untrusted texture files.  Explicit regressions next to the ASan/UBSan fuzzer
+    (tests/test_sanitize_host.py): an 8-bit BMP whose palette would lie beyond the end of the file, a BMP with a pixel
+    offset past the end, a PFM that ends inside its header, PNM / PFM / EXR headers with absurd dimensions."""
+    def refused(name, data):
+        p = tmp_path / name
+        open(p, "wb").write(data)
+        with pytest.raises(hostlib.HostError):
+            hostlib.load_image(str(p))
+    info = struct.pack("<IiiHHIIiiII", 40, 4, 2, 1, 8, 0, 8, 0, 0, 0, 0)
+    refused("pal.bmp", b"BM" + struct.pack("<IHHI", 62, 0, 0, 54) + info + bytes(8))                 # 8 bpp, no palette in the file
+    refused("hdr.bmp", b"BM" + struct.pack("<IHHI", 62, 0, 0, 54) + struct.pack("<IiiHHIIiiII", 0x7fffff00, 4, 2, 1, 8, 0, 8, 0, 0, 0, 0) + bytes(8))
+    refused("off.bmp", b"BM" + struct.pack("<IHHI", 62, 0, 0, 0xfffffff0) + struct.pack("<IiiHHIIiiII", 40, 4, 2, 1, 24, 0, 8, 0, 0, 0, 0) + bytes(32))
+    refused("neg.bmp", b"BM" + struct.pack("<IHHI", 62, 0, 0, 54) + struct.pack("<IiiHHIIiiII", 40, 4, -2147483648, 1, 24, 0, 8, 0, 0, 0, 0) + bytes(32))
+    refused("short.pfm", b"PF\n1")
+    refused("tiny.pfm", b"PF")
+    refused("huge.pfm", b"PF\n99999999 99999999\n-1.0\n" + bytes(64))
+    refused("huge.ppm", b"P6\n99999999999999999999 5\n255\n" + bytes(64))
+    refused("wide.ppm", b"P6\n70000 70000\n255\n" + bytes(64))
+    good = T_exr_small()
+    bad = bytearray(good)
+    k = bad.index(b"dataWindow") + len(b"dataWindow\0box2i\0") + 4
+    bad[k + 8:k + 12] = struct.pack("<i", 0x7ffffff0)                                                # xMax
+    refused("window.exr", bytes(bad))
+
+
+def T_exr_small():
+    return exr_file(np.random.RandomState(1).rand(3, 4, 3).astype(np.float32), 0)
