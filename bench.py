@@ -212,6 +212,15 @@ def cpu_leg(mesh_tag, mesh, seconds_target, steps, warmup, want_line, keep=None)
     return base, total / steps * 1e3, info
 
 
+def make_config(args, info, N):
+    """The `config` object of the JSON line: identical for the product arm and the reference arm (the driver compares them)."""
+    S = args.spp_per_step
+    return {"workload": WORKLOAD, "mesh": args.mesh, "n_tris": info["n_tris"], "n_spheres": info["n_spheres"],
+            "spp_per_step": S, "frames_per_gpu_per_step": S,
+            "sharding": f"sample-interleaved x{N} + one ncclReduce(sum, fp32, root 0) per step issued by pb_render (PB_RENDER_REDUCE)" if N > 1 else "none",
+            "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"}
+
+
 def reference_main(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -220,7 +229,8 @@ def reference_main(args):
     line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": "Msamples/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "mesh": args.mesh, "n_tris": info["n_tris"], "n_spheres": info["n_spheres"]},
+            "config": make_config(args, info, max(1, int(os.environ.get("WORLD_SIZE", str(args.gpus))))),   # the product arm's config: same workload;
+            # each reference step is a bounded sample of it (cpu_baseline.sample says which)
             "mrays_per_s": base["mrays_per_s"], "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -527,9 +537,7 @@ def product_main(args):
         line = {"metric": METRIC, "value": value, "unit": "Msamples/s", "n_gpus": N, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "mesh": args.mesh, "n_tris": info["n_tris"], "n_spheres": info["n_spheres"],
-                           "spp_per_step": S, "frames_per_gpu_per_step": S, "sharding": f"sample-interleaved x{N} + one ncclReduce(sum, fp32, root 0) per step issued by pb_render (PB_RENDER_REDUCE)" if N > 1 else "none",
-                           "l2": "inputs larger than L2 (BVH + primitives ~0.7 GB, path state > 1 GB per wave)"},
+                "config": make_config(args, info, N),
                 "mrays_per_s": mrays, "rays_per_sample": (rays_c_all + rays_a_all) / samples,
                 "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "api": "pb_render(PB_RENDER_HOST_BUFFERS | PB_RENDER_ASYNC) x steps + pb_wait", "host_enqueue_ms_each": e2e_async_host,
