@@ -15,6 +15,7 @@ constexpr int kTraceThreads = 128;
 
 template<bool ANY>
 struct RayIO {
+    static constexpr bool kFixedRange = false;
     const float4* __restrict__ rays;
     float4* __restrict__ hits;
     uint8_t* __restrict__ occ;
@@ -34,7 +35,7 @@ template<bool ANY, bool COUNT>
 __global__ void __launch_bounds__(kTraceThreads)
 k_trace(TraceScene sc, const float4* __restrict__ rays, uint32_t n, float4* __restrict__ hits,
         uint8_t* __restrict__ occ, unsigned long long* __restrict__ counters) {
-    __shared__ U2 s_stack[PB_SMEM_STACK * kTraceThreads];
+    __shared__ U2 s_stack[(PB_SMEM_STACK + PB_COLD_ENTRIES) * kTraceThreads];
     U2 tail[PB_LOCAL_STACK];
     LaneStack st;
     st.init(s_stack + threadIdx.x, kTraceThreads, tail);

@@ -11,6 +11,7 @@
 //   bool load(uint32_t i, V3& o, V3& d, float& tmin, float& tmax)   ray i of the queue (false = skip)
 //   void store(uint32_t i, const Hit& h)                             result of ray i (any lane, any time)
 //   void flush()                                                     warp-converged point after a batch of stores
+//   static constexpr bool kFixedRange                                every ray runs over [kPathTmin, kPathTmax] (path rays)
 #pragma once
 #include "pb_traverse.cuh"
 
@@ -28,7 +29,7 @@ template<bool ANY, bool COUNT, class IO>
 __device__ __forceinline__ void trace_loop(const TraceScene& sc, IO& io, LaneStack& st, uint32_t* cursor, uint32_t n,
                                            uint32_t refill, TraceCounters& tc) {
     const unsigned lane = threadIdx.x & 31u;
-    Traversal<ANY, COUNT> tr;
+    Traversal<ANY, COUNT, IO::kFixedRange> tr;
     bool have = false, exhausted = false, pending = false;   // pending: tr.best of ray idx is finished and not yet stored
     uint32_t idx = 0;
     while (true) {
@@ -40,13 +41,13 @@ __device__ __forceinline__ void trace_loop(const TraceScene& sc, IO& io, LaneSta
                 if ((int)lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(need));
                 base = __shfl_sync(0xFFFFFFFFu, base, leader);
                 if (!have) {
-                    if (PB_DEFER_STORE && pending) { io.store(idx, tr.best); pending = false; }
+                    if (PB_DEFER_STORE && pending) { io.store(idx, tr.result(st)); pending = false; }
                     idx = base + (uint32_t)__popc(need & ((1u << lane) - 1u));
                     if (idx < n) {
                         V3 o, d; float tmin, tmax;
                         if (io.load(idx, o, d, tmin, tmax)) {
                             tr.begin(sc, o, d, tmin, tmax, st);
-                            if (tr.finished_at_begin()) io.store(idx, tr.best);
+                            if (tr.finished_at_begin()) io.store(idx, tr.result(st));
                             else have = true;
                         }
                     }
@@ -56,7 +57,7 @@ __device__ __forceinline__ void trace_loop(const TraceScene& sc, IO& io, LaneSta
             }
         }
         if (!__any_sync(0xFFFFFFFFu, have)) {
-            if (PB_DEFER_STORE && pending) { io.store(idx, tr.best); pending = false; }
+            if (PB_DEFER_STORE && pending) { io.store(idx, tr.result(st)); pending = false; }
             io.flush();
             if (exhausted) break;
             continue;
@@ -64,14 +65,14 @@ __device__ __forceinline__ void trace_loop(const TraceScene& sc, IO& io, LaneSta
         while (true) {
             if (tr.step(sc, st, &tc, have)) {   // all lanes call step()
                 have = false;
-                if (PB_DEFER_STORE) pending = true; else io.store(idx, tr.best);
+                if (PB_DEFER_STORE) pending = true; else io.store(idx, tr.result(st));
             }
             const unsigned m = __ballot_sync(0xFFFFFFFFu, have);
             if (m == 0u || (!exhausted && (uint32_t)__popc(m) < refill)) break;
         }
         if (!PB_DEFER_STORE) io.flush();
         else if (exhausted) {   // no refill will come: write what finished, bin it
-            if (pending) { io.store(idx, tr.best); pending = false; }
+            if (pending) { io.store(idx, tr.result(st)); pending = false; }
             io.flush();
         }
     }

@@ -54,6 +54,17 @@ inline int pop_cnt(uint32_t x) { return __builtin_popcount(x); }
 #define PB_SMEM_STACK 12
 #endif
 #define PB_LOCAL_STACK 52
+// PB_COLD_SMEM (default): the per-ray state the node loop never touches - direction, u, v, object of the best hit -
+// lives in three more 64-bit shared-memory entries behind the lane's stack instead of in registers, and path rays'
+// constant [tmin, tmax] are compile-time constants (Traversal<.., FIXED>).  At 64 registers k_extend then has no
+// compiler spills (it had 24 / 32 B in the node loop): 545.4 against 530.7 Msamples/s on the same box (+2.8 %,
+// profiles/r02_extend.md, call J).  Capping at 56 registers for a 9th resident CTA still spills 40 / 48 B and loses
+// (519 Msamples/s), so kTraceMinBlocks stays 8.  Results are identical either way; 0 = the register-only layout.
+#ifndef PB_COLD_SMEM
+#define PB_COLD_SMEM 1
+#endif
+#define PB_COLD_ENTRIES (PB_COLD_SMEM ? 3 : 0)
+constexpr float kPathTmin = 0.001f, kPathTmax = 1e16f;   // main.cu:77-82,158-163
 
 struct U2 { uint32_t x, y; };
 
@@ -74,6 +85,8 @@ struct LaneStack {
         --sp;
         return sp < PB_SMEM_STACK ? smem[sp * stride] : local[sp - PB_SMEM_STACK];
     }
+    // cold entries behind the stack head (PB_COLD_SMEM): k = 0 (d.x, d.y), 1 (d.z, u), 2 (v, object)
+    PB_HD U2& cold(int k) { return smem[(PB_SMEM_STACK + k) * stride]; }
 };
 
 // Quantised plane byte -> float without a conversion instruction: one PRMT drops byte J of w into
@@ -233,10 +246,13 @@ PB_HD uint32_t node_hits(const U4& n0, const U4& n1, const U4& n2, const U4& n3,
 // least `prim_batch` lanes of the warp hold primitives or no lane can advance through nodes any
 // more; the primitive tests then run with many lanes instead of the 2.6 / 32 measured before
 // (profiles/r01_extend.md).
-template<bool ANY, bool COUNT>
+template<bool ANY, bool COUNT, bool FIXED = false>
 struct Traversal {
     V3 o, d;
-    float tmin, tmax;   // tmax = the ray's own bound (ties on t need it; best.t only orders)
+    float tmin_, tmax_;   // tmax = the ray's own bound (ties on t need it; best.t only orders); unused (and therefore not
+                          // kept in registers) when FIXED: path rays always run over [kPathTmin, kPathTmax]
+    PB_HD float tmin() const { return FIXED ? kPathTmin : tmin_; }
+    PB_HD float tmax() const { return FIXED ? kPathTmax : tmax_; }
     V3 id;              // 1 / d (RayPre::id); RayPre::noid is re-derived in the primitive phase (3 registers less)
     uint32_t op;        // oct_perm(octinv): octinv in the low byte
     U2 G, P;            // pending node group / primitive group.  G.y = inner hits << 24 | pmask[0..15] << 8 | imask,
@@ -245,17 +261,28 @@ struct Traversal {
                         // pmask bits that nothing reads
     Hit best;
 
-    PB_HD void begin(const TraceScene& sc, V3 o_, V3 d_, float tmin_, float tmax_, LaneStack& st) {
-        o = o_; d = d_; tmin = tmin_; tmax = tmax_;
-        best.t = tmax_; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu; best.obj = 0xFFFFFFFFu;
-        id = ray_pre(o, d).id;
-        const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
+    PB_HD void begin(const TraceScene& sc, V3 o_, V3 d_, float tmin_in, float tmax_in, LaneStack& st) {
+        o = o_; d = d_; tmin_ = tmin_in; tmax_ = tmax_in;
+        best.t = tmax(); best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu; best.obj = 0xFFFFFFFFu;
+        id = ray_pre(o, d_).id;
+        const uint32_t oct = (d_.x < 0.f ? 4u : 0u) | (d_.y < 0.f ? 2u : 0u) | (d_.z < 0.f ? 1u : 0u);
+        if (PB_COLD_SMEM) {
+            st.cold(0) = {f2u(d_.x), f2u(d_.y)};
+            st.cold(1) = {f2u(d_.z), 0u};
+            st.cold(2) = {0u, 0xFFFFFFFFu};
+        }
         op = oct_perm(7u - oct);
         G = {0u, sc.n_nodes ? 0x80000000u : 0u};
         P = {0u, 0u};
         st.sp = 0;
     }
     PB_HD bool finished_at_begin() const { return (G.y & 0xff000000u) == 0u; }
+    // the result of a finished ray (cold members come back from shared memory)
+    PB_HD Hit result(LaneStack& st) const {
+        Hit h = best;
+        if (PB_COLD_SMEM && !ANY) { const U2 c1 = st.cold(1), c2 = st.cold(2); h.u = u2f(c1.y); h.v = u2f(c2.x); h.obj = c2.y; }
+        return h;
+    }
 
     // returns true when the ray is finished (best holds the result); `alive` = this lane holds a ray
     PB_HD bool step(const TraceScene& sc, LaneStack& st, TraceCounters* cnt, bool alive) {
@@ -269,7 +296,7 @@ struct Traversal {
             const U4* np = sc.nodes + 5ull * (G.x + rel);
             const U4 n0 = ld_u4(np), n1 = ld_u4(np + 1), n2 = ld_u4(np + 2), n3 = ld_u4(np + 3), n4 = ld_u4(np + 4);
             if (COUNT) cnt->nodes++;
-            const uint32_t hits = node_hits(n0, n1, n2, n3, n4, o, id, op, tmin, best.t, sc.k47);
+            const uint32_t hits = node_hits(n0, n1, n2, n3, n4, o, id, op, tmin(), best.t, sc.k47);
             G.x = n1.x;
             G.y = pack_g(hits, n1.z, n0.w);
             P.x = n1.y;
@@ -285,6 +312,8 @@ struct Traversal {
         if (has_p && do_prims) {
             uint32_t iters = sc.prim_iters;
             const RayPre pre = {id, {-f_mul(o.x, id.x), -f_mul(o.y, id.y), -f_mul(o.z, id.z)}};   // == ray_pre(o, d), bit for bit
+            V3 dd = d;
+            if (PB_COLD_SMEM) { const U2 c0 = st.cold(0), c1 = st.cold(1); dd = {u2f(c0.x), u2f(c0.y), u2f(c1.x)}; }
             do {
                 const int i = lo_bit(P.y);
                 P.y &= P.y - 1u;
@@ -293,10 +322,14 @@ struct Traversal {
                 r.a = ld_v4(pp); r.b = ld_v4(pp + 1); r.c = ld_v4(pp + 2);
                 if (COUNT) { if (f2u(r.c.w) == PRIM_TRI) cnt->tris++; else cnt->spheres++; }
                 float t, u, v;
-                if (prim_accept(r, sc.objs, o, d, pre, tmin, tmax, best.t, sc.delta, t, u, v)) {
+                if (prim_accept(r, sc.objs, o, dd, pre, tmin(), tmax(), best.t, sc.delta, t, u, v)) {
                     const uint32_t id = f2u(r.a.w);
                     if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); P.y = 0u; return true; }
-                    if (t < best.t || (t == best.t && id < best.prim)) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); }
+                    if (t < best.t || (t == best.t && id < best.prim)) {
+                        best.t = t; best.prim = id;
+                        if (PB_COLD_SMEM) { st.cold(1).y = f2u(u); st.cold(2) = {f2u(v), f2u(r.b.w)}; }
+                        else { best.u = u; best.v = v; best.obj = f2u(r.b.w); }
+                    }
                 }
             } while ((P.y & 0x00ffffffu) && --iters);
         }
@@ -314,7 +347,7 @@ PB_HD void traverse(const TraceScene& sc, V3 o, V3 d, float tmin, float tmax, Hi
     tr.begin(sc, o, d, tmin, tmax, st);
     if (!tr.finished_at_begin())
         while (!tr.step(sc, st, cnt, true)) {}
-    best = tr.best;
+    best = tr.result(st);
 }
 
 }  // namespace pb

@@ -31,7 +31,7 @@ constexpr int kWfThreads = 128;
 enum { C_EXT_A = 0, C_EXT_B = 1, C_SHADOW = 2, C_MAT0 = 3 /* ..10 */, C_CUR_EXT = 11, C_CUR_CON = 12, C_FRAME0 = 13, C_COUNT = 16 };
 enum : uint32_t { F_DEPTH_MASK = 0xffffu, F_DELTA = 0x80000000u };   // depth <= kMaxDepthLimit fits 16 bits
 constexpr uint32_t kMaxDepthLimit = 1024u;
-constexpr float kRayTmin = 0.001f, kRayTmax = 1e16f;
+constexpr float kRayTmin = kPathTmin, kRayTmax = kPathTmax;
 // Queue entries are visited in (increasingly random) queue order, so the first touch of a path record is a
 // DRAM round trip that nothing in the warp can overlap.  Every consumer therefore asks L2 for the records
 // of the entries a fixed distance AHEAD of the ones it is about to use (prefetch.global.L2: no register, no
@@ -172,6 +172,7 @@ __global__ void __launch_bounds__(256) k_generate(WfState s, WfScene sc, uint32_
 
 // ---- extend: closest hit for every queued path, then bin by material --------------------------------
 struct ExtendIO {
+    static constexpr bool kFixedRange = true;    // path rays: tmin / tmax are the constants of main.cu:77-82,158-163
     WfState s;
     const ObjRec* __restrict__ objs;
     const MatRec* __restrict__ mats;
@@ -210,7 +211,7 @@ struct ExtendIO {
 
 template<bool COUNT>
 __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_extend(WfState s, WfScene sc, int cur) {
-    __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
+    __shared__ U2 s_stack[(PB_SMEM_STACK + PB_COLD_ENTRIES) * kWfThreads];
     U2 tail[PB_LOCAL_STACK];
     LaneStack st;
     st.init(s_stack + threadIdx.x, kWfThreads, tail);
@@ -223,6 +224,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_extend(WfSt
 
 // ---- connect: any hit for the shadow queue; unoccluded contributions go to the path radiance --------
 struct ConnectIO {
+    static constexpr bool kFixedRange = false;
     WfState s;
     uint32_t n;
     __device__ __forceinline__ bool load(uint32_t i, V3& o, V3& d, float& tmin, float& tmax) const {
@@ -250,7 +252,7 @@ struct ConnectIO {
 
 template<bool COUNT>
 __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfState s, WfScene sc) {
-    __shared__ U2 s_stack[PB_SMEM_STACK * kWfThreads];
+    __shared__ U2 s_stack[(PB_SMEM_STACK + PB_COLD_ENTRIES) * kWfThreads];
     U2 tail[PB_LOCAL_STACK];
     LaneStack st;
     st.init(s_stack + threadIdx.x, kWfThreads, tail);

@@ -133,7 +133,7 @@ static TraceScene scene_of(HS* h) {
 }
 void hs_trace_closest(HS* h, const float* rays, uint64_t n, float* hits /* t,u,v,prim bits */) {
     TraceScene sc = scene_of(h);
-    U2 smem[PB_SMEM_STACK];
+    U2 smem[PB_SMEM_STACK + PB_COLD_ENTRIES];
     U2 tail[PB_LOCAL_STACK];
     LaneStack st;
     st.init(smem, 1, tail);
@@ -147,7 +147,7 @@ void hs_trace_closest(HS* h, const float* rays, uint64_t n, float* hits /* t,u,v
 }
 void hs_trace_any(HS* h, const float* rays, uint64_t n, uint8_t* occ) {
     TraceScene sc = scene_of(h);
-    U2 smem[PB_SMEM_STACK];
+    U2 smem[PB_SMEM_STACK + PB_COLD_ENTRIES];
     U2 tail[PB_LOCAL_STACK];
     LaneStack st;
     st.init(smem, 1, tail);
