@@ -25,6 +25,10 @@ constexpr int kWfThreads = 128;
 #ifndef PB_SHADE_MIN_BLOCKS
 #define PB_SHADE_MIN_BLOCKS 8   // 64 registers: 28.8 vs 30.0 ms of shading per C4 step at 5 CTAs (80-96 registers)
 #endif
+#ifndef PB_SHADE_MIN_BLOCKS_SMOOTH
+#define PB_SHADE_MIN_BLOCKS_SMOOTH PB_SHADE_MIN_BLOCKS   // diffuse / dielectric / conductor (materials 1, 2, 4); 9 / 10 CTAs measured slower (profiles/r02_extend.md, call K)
+#endif
+constexpr int shade_min_blocks(int mat) { return (mat == 1 || mat == 2 || mat == 4) ? PB_SHADE_MIN_BLOCKS_SMOOTH : PB_SHADE_MIN_BLOCKS; }
 #ifndef PB_TRACE_MIN_BLOCKS
 #define PB_TRACE_MIN_BLOCKS 8   // 64 registers per thread
 #endif
@@ -266,7 +270,7 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfS
 
 // ---- shade<MAT>: one path vertex.  Follows main.cu:84-183 line by line -----------------------------------
 template<int MAT>
-__global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfState s, WfScene sc, int cur) {
+__global__ void __launch_bounds__(kWfThreads, shade_min_blocks(MAT)) k_shade(WfState s, WfScene sc, int cur) {
     const uint32_t n = s.cnt[C_MAT0 + MAT];
     const uint32_t* q = s.q_mat + (size_t)MAT * s.cap;
     uint32_t* qnext = cur ? s.q_ext[0] : s.q_ext[1];
