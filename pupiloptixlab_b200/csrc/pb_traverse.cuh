@@ -322,7 +322,7 @@ struct Traversal {
                 r.a = ld_v4(pp); r.b = ld_v4(pp + 1); r.c = ld_v4(pp + 2);
                 if (COUNT) { if (f2u(r.c.w) == PRIM_TRI) cnt->tris++; else cnt->spheres++; }
                 float t, u, v;
-                if (prim_accept(r, sc.objs, o, dd, pre, tmin(), tmax(), best.t, sc.delta, t, u, v)) {
+                if (prim_accept(r, sc.objs, o, dd, pre, tmin(), tmax(), best.t, sc.delta, t, u, v, PB_TRI_TEST_FIRST && !ANY)) {
                     const uint32_t id = f2u(r.a.w);
                     if (ANY) { best.t = t; best.u = u; best.v = v; best.prim = id; best.obj = f2u(r.b.w); P.y = 0u; return true; }
                     if (t < best.t || (t == best.t && id < best.prim)) {
