@@ -29,6 +29,9 @@ constexpr int kWfThreads = 128;
 #define PB_SHADE_MIN_BLOCKS_SMOOTH PB_SHADE_MIN_BLOCKS   // diffuse / dielectric / conductor (materials 1, 2, 4); 9 / 10 CTAs measured slower (profiles/r02_extend.md, call K)
 #endif
 constexpr int shade_min_blocks(int mat) { return (mat == 1 || mat == 2 || mat == 4) ? PB_SHADE_MIN_BLOCKS_SMOOTH : PB_SHADE_MIN_BLOCKS; }
+#ifndef PB_SHADE_PREFETCH
+#define PB_SHADE_PREFETCH 0
+#endif
 #ifndef PB_TRACE_MIN_BLOCKS
 #define PB_TRACE_MIN_BLOCKS 8   // 64 registers per thread
 #endif
@@ -277,14 +280,34 @@ __global__ void __launch_bounds__(kWfThreads, shade_min_blocks(MAT)) k_shade(WfS
     uint32_t* next_count = &s.cnt[cur ? C_EXT_A : C_EXT_B];
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
-    // (Requesting the next iterations' records from L2 ahead of time was tried and is slower: these kernels are
-    // bound by L1 passes per scattered request, not by exposed latency - profiles/r01_shade.md.)
+    // Requesting the next iteration's record ahead of time (PB_SHADE_PREFETCH = 1: prefetch.global.L2, 2: .L1) is slower:
+    // 32.2 against 27.3 ms of shading per C4 step (round 2, call R; round 1 measured the same on an older layout).  The
+    // prefetch pulls whole lines where the loads take three sectors: these kernels run at the DRAM rate of scattered
+    // sectors, not on exposed latency (profiles/r01_shade.md, r02_extend.md).
+#if PB_SHADE_PREFETCH
+    // two queue entries ahead: the record of the NEXT iteration is requested (prefetch.global.L2 / .L1) at the head of this one
+    const uint32_t stride = n_warps * 32u;
+    uint32_t s1 = warp * 32u + lane + stride < n ? q[warp * 32u + lane + stride] : 0xFFFFFFFFu;
+#endif
     for (uint32_t base = warp * 32u; base < n; base += n_warps * 32u) {
         const uint32_t i = base + lane;
         bool push_ray = false, push_shadow = false;
         uint32_t slot = 0;
         V3 sh_o = v3(0.f), sh_d = v3(0.f), contrib = v3(0.f);
         float sh_tmax = 0.f;
+#if PB_SHADE_PREFETCH
+        if (s1 != 0xFFFFFFFFu) {
+            const float4* nr = s.rec + (size_t)R_COUNT * s1;
+#if PB_SHADE_PREFETCH == 2
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(nr));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(nr + 4));
+#else
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(nr));
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(nr + 4));
+#endif
+        }
+        s1 = (i + 2u * stride < n) ? q[i + 2u * stride] : 0xFFFFFFFFu;
+#endif
         if (i < n) {
             slot = q[i];
             float4* rec = s.rec + (size_t)R_COUNT * slot;
