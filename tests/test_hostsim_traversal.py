@@ -93,3 +93,34 @@ def test_tree_shape_knobs_do_not_change_results(hostsim_lib, oracle_api, leaf_ma
     finally:
         hostsim_lib.hs_set_leaf_max(2)
         hostsim_lib.hs_set_bottom_max(8)
+
+
+@pytest.mark.parametrize("flags", ["-DPB_COLD_SMEM=0 -DPB_TRI_TEST_FIRST=0 -DPB_SPHERE_TEST_FIRST=0",
+                                   "-DPB_COLD_SMEM=1 -DPB_TRI_TEST_FIRST=1 -DPB_BEHIND_BEST_EARLY=1"])
+def test_compile_time_switches_do_not_change_results(oracle_api, flags, tmp_path):
+    """PB_COLD_SMEM (cold ray state behind the shared-memory stack), PB_TRI_TEST_FIRST / PB_SPHERE_TEST_FIRST (primitive test
+    before the slab of its padded box) and PB_BEHIND_BEST_EARLY change instruction order and register use, never the accepted
+    set: the kernels' bodies built with the switches off and with all of them on return the oracle's brute-force hits bit for bit."""
+    import os
+    import subprocess
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "hostsim")
+    so = str(tmp_path / "libhostsim_variant.so")
+    fma = ["-mfma"] if "fma" in open("/proc/cpuinfo").read() else []
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", *fma, "-shared", "-Wno-unknown-pragmas",
+                           *flags.split(), "-o", so, os.path.join(d, "hostsim.cpp")])
+    lib = C.CDLL(so)
+    pos, idx, sph = U.random_soup(3000, 80, 21)
+    o = pyoracle.OracleContext(oracle_api)
+    U.oracle_scene(o, pos, idx, sph)
+    rays = U.random_rays(8000, 121)
+    rays["tmax"][::3] = 1.5
+    want = o.trace_closest_brute(rays)
+    h = hs_build(lib, pos, idx, sph)
+    got = hs_closest(lib, h, rays)
+    assert np.array_equal(got["prim"], want["prim"])
+    hit = want["prim"] != capi.MISS
+    assert hit.sum() > 1000
+    for f in ("t", "u", "v"):
+        assert np.array_equal(got[f][hit].view(np.uint32), want[f][hit].view(np.uint32))
+    assert np.array_equal(hs_any(lib, h, rays), o.trace_any_brute(rays))
+    lib.hs_destroy(h)
