@@ -128,10 +128,8 @@ PB_HD void pad_box(V3& lo, V3& hi, float d) {
 #endif
 #ifndef PB_TRI_TEST_FIRST
 #define PB_TRI_TEST_FIRST 1      // closest-hit rays only (Traversal passes tri_first = !ANY): same-box A/B on C4, twice: 542.0 -> 546.0 Msamples/s;
-#endif                           // for any-hit rays too: k_connect 19.4 -> 19.7 ms per step (profiles/r02_extend.md, calls N and O)
-#ifndef PB_BEHIND_BEST_EARLY
-#define PB_BEHIND_BEST_EARLY 0   // rejecting t > t_best before the box of a test-first primitive: 525.5 (8 / 12 B of spills in k_extend), not adopted
-#endif
+#endif                           // for any-hit rays too: k_connect 19.4 -> 19.7 ms per step; rejecting t > t_best before the box as well:
+                                 // 525.5 (spills) - profiles/r02_extend.md, calls N and O
 PB_HD bool prim_accept(const PrimRec& r, const ObjRec* objs, V3 o, V3 d, const RayPre& pre, float tmin, float tmax,
                        float t_best, float delta, float& t, float& u, float& v, bool tri_first = false) {
     V3 lo, hi;
@@ -142,7 +140,6 @@ PB_HD bool prim_accept(const PrimRec& r, const ObjRec* objs, V3 o, V3 d, const R
         // only drops hits behind the current best (they lose the (t, id) comparison anyway).
         u = 0.f; v = 0.f;
         if (!sphere_test_uniform(o, d, tmin, tmax, r.b.y, {r.c.x, r.c.y, r.c.z}, t)) return false;
-        if (PB_BEHIND_BEST_EARLY && t > t_best) return false;   // loses the (t, id) comparison whatever its box says
         prim_bbox(r, lo, hi);
         pad_box(lo, hi, delta);
         float N, F;
@@ -153,7 +150,6 @@ PB_HD bool prim_accept(const PrimRec& r, const ObjRec* objs, V3 o, V3 d, const R
         // the same argument for triangles: Moeller-Trumbore rejects on u after about as many instructions as the slab
         // prologue takes, and only hits pay for the padded box (a warp runs this branch with 2-3 lanes)
         if (!tri_test(o, d, tmin, tmax, {r.a.x, r.a.y, r.a.z}, {r.b.x, r.b.y, r.b.z}, {r.c.x, r.c.y, r.c.z}, t, u, v)) return false;
-        if (PB_BEHIND_BEST_EARLY && t > t_best) return false;
         prim_bbox(r, lo, hi);
         pad_box(lo, hi, delta);
         float N, F;

@@ -60,9 +60,6 @@ inline int pop_cnt(uint32_t x) { return __builtin_popcount(x); }
 // compiler spills (it had 24 / 32 B in the node loop): 545.4 against 530.7 Msamples/s on the same box (+2.8 %,
 // profiles/r02_extend.md, call J).  Capping at 56 registers for a 9th resident CTA still spills 40 / 48 B and loses
 // (519 Msamples/s), so kTraceMinBlocks stays 8.  Results are identical either way; 0 = the register-only layout.
-#ifndef PB_PRIM_PREFETCH
-#define PB_PRIM_PREFETCH 0   // 1 / 2: request the first primitive record (L1 / L2) when the node visit finds it.  k_extend 72.4 -> 75.1 ms per
-#endif                       // C4 step (call U): the wait on the record is hidden by other warps, the extra instructions are not
 #ifndef PB_COLD_SMEM
 #define PB_COLD_SMEM 1
 #endif
@@ -304,18 +301,6 @@ struct Traversal {
             G.y = pack_g(hits, n1.z, n0.w);
             P.x = n1.y;
             P.y = pack_p(hits, n1.z);
-#if defined(__CUDA_ARCH__) && PB_PRIM_PREFETCH
-            // the first primitive this lane will test: requested now, tested when the warp's batch forms (or at once)
-            if (P.y & 0x00ffffffu) {
-                const int i0 = lo_bit(P.y);
-                const V4* pp0 = sc.prims + 3ull * (P.x + (uint32_t)pop_cnt(n1.z & ((1u << i0) - 1u)));
-#if PB_PRIM_PREFETCH == 2
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(pp0));
-#else
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(pp0));
-#endif
-            }
-#endif
         }
         const bool has_p = alive && (P.y & 0x00ffffffu) != 0u;
 #if defined(__CUDA_ARCH__)

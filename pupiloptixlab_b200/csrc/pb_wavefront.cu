@@ -23,14 +23,8 @@ namespace pb {
 
 constexpr int kWfThreads = 128;
 #ifndef PB_SHADE_MIN_BLOCKS
-#define PB_SHADE_MIN_BLOCKS 8   // 64 registers: 28.8 vs 30.0 ms of shading per C4 step at 5 CTAs (80-96 registers)
-#endif
-#ifndef PB_SHADE_MIN_BLOCKS_SMOOTH
-#define PB_SHADE_MIN_BLOCKS_SMOOTH PB_SHADE_MIN_BLOCKS   // diffuse / dielectric / conductor (materials 1, 2, 4); 9 / 10 CTAs measured slower (profiles/r02_extend.md, call K)
-#endif
-constexpr int shade_min_blocks(int mat) { return (mat == 1 || mat == 2 || mat == 4) ? PB_SHADE_MIN_BLOCKS_SMOOTH : PB_SHADE_MIN_BLOCKS; }
-#ifndef PB_SHADE_PREFETCH
-#define PB_SHADE_PREFETCH 0
+#define PB_SHADE_MIN_BLOCKS 8   // 64 registers: 28.8 vs 30.0 ms of shading per C4 step at 5 CTAs (80-96 registers); per material, 9 / 10 CTAs for the
+                                // smooth ones and 6 for the rough ones are slower as well (profiles/r02_extend.md, call K)
 #endif
 #ifndef PB_TRACE_MIN_BLOCKS
 #define PB_TRACE_MIN_BLOCKS 8   // 64 registers per thread
@@ -273,41 +267,23 @@ __global__ void __launch_bounds__(kWfThreads, PB_TRACE_MIN_BLOCKS) k_connect(WfS
 
 // ---- shade<MAT>: one path vertex.  Follows main.cu:84-183 line by line -----------------------------------
 template<int MAT>
-__global__ void __launch_bounds__(kWfThreads, shade_min_blocks(MAT)) k_shade(WfState s, WfScene sc, int cur) {
+__global__ void __launch_bounds__(kWfThreads, PB_SHADE_MIN_BLOCKS) k_shade(WfState s, WfScene sc, int cur) {
     const uint32_t n = s.cnt[C_MAT0 + MAT];
     const uint32_t* q = s.q_mat + (size_t)MAT * s.cap;
     uint32_t* qnext = cur ? s.q_ext[0] : s.q_ext[1];
     uint32_t* next_count = &s.cnt[cur ? C_EXT_A : C_EXT_B];
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
-    // Requesting the next iteration's record ahead of time (PB_SHADE_PREFETCH = 1: prefetch.global.L2, 2: .L1) is slower:
+    // Requesting the next iteration's record ahead of time (prefetch.global.L2 or .L1, two queue entries ahead) is slower:
     // 32.2 against 27.3 ms of shading per C4 step (round 2, call R; round 1 measured the same on an older layout).  The
     // prefetch pulls whole lines where the loads take three sectors: these kernels run at the DRAM rate of scattered
     // sectors, not on exposed latency (profiles/r01_shade.md, r02_extend.md).
-#if PB_SHADE_PREFETCH
-    // two queue entries ahead: the record of the NEXT iteration is requested (prefetch.global.L2 / .L1) at the head of this one
-    const uint32_t stride = n_warps * 32u;
-    uint32_t s1 = warp * 32u + lane + stride < n ? q[warp * 32u + lane + stride] : 0xFFFFFFFFu;
-#endif
     for (uint32_t base = warp * 32u; base < n; base += n_warps * 32u) {
         const uint32_t i = base + lane;
         bool push_ray = false, push_shadow = false;
         uint32_t slot = 0;
         V3 sh_o = v3(0.f), sh_d = v3(0.f), contrib = v3(0.f);
         float sh_tmax = 0.f;
-#if PB_SHADE_PREFETCH
-        if (s1 != 0xFFFFFFFFu) {
-            const float4* nr = s.rec + (size_t)R_COUNT * s1;
-#if PB_SHADE_PREFETCH == 2
-            asm volatile("prefetch.global.L1 [%0];" :: "l"(nr));
-            asm volatile("prefetch.global.L1 [%0];" :: "l"(nr + 4));
-#else
-            asm volatile("prefetch.global.L2 [%0];" :: "l"(nr));
-            asm volatile("prefetch.global.L2 [%0];" :: "l"(nr + 4));
-#endif
-        }
-        s1 = (i + 2u * stride < n) ? q[i + 2u * stride] : 0xFFFFFFFFu;
-#endif
         if (i < n) {
             slot = q[i];
             float4* rec = s.rec + (size_t)R_COUNT * slot;

@@ -96,10 +96,10 @@ def test_tree_shape_knobs_do_not_change_results(hostsim_lib, oracle_api, leaf_ma
 
 
 @pytest.mark.parametrize("flags", ["-DPB_COLD_SMEM=0 -DPB_TRI_TEST_FIRST=0 -DPB_SPHERE_TEST_FIRST=0",
-                                   "-DPB_COLD_SMEM=1 -DPB_TRI_TEST_FIRST=1 -DPB_BEHIND_BEST_EARLY=1"])
+                                   "-DPB_COLD_SMEM=1 -DPB_TRI_TEST_FIRST=1 -DPB_SPHERE_TEST_FIRST=1"])
 def test_compile_time_switches_do_not_change_results(oracle_api, flags, tmp_path):
     """PB_COLD_SMEM (cold ray state behind the shared-memory stack), PB_TRI_TEST_FIRST / PB_SPHERE_TEST_FIRST (primitive test
-    before the slab of its padded box) and PB_BEHIND_BEST_EARLY change instruction order and register use, never the accepted
+    before the slab of its padded box) change instruction order and register use, never the accepted
     set: the kernels' bodies built with the switches off and with all of them on return the oracle's brute-force hits bit for bit."""
     import os
     import subprocess
